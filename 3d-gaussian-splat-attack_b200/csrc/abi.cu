@@ -1,0 +1,218 @@
+// abi.cu -- extern "C" entry points declared in include/gsr_b200.h (orchestration only).
+//
+// Replaces the host side of CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+// (DGR/cuda_rasterizer/rasterizer_impl.cu:141-153,198-433) and the pybind glue
+// (DGR/rasterize_points.cu:35-217).  No allocation, no torch: the caller owns every buffer.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include "common.cuh"
+
+namespace gsr {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+static int check_inputs(const gsr_inputs* in) {
+  if (!in) { set_error("inputs is NULL"); return GSR_ERR_INVALID; }
+  if (in->P < 0 || in->W <= 0 || in->H <= 0) { set_error("bad sizes P=%d W=%d H=%d", in->P, in->W, in->H); return GSR_ERR_INVALID; }
+  if (in->W > 65535 * TILE_X || in->H > 65535 * TILE_Y) { set_error("image too large"); return GSR_ERR_INVALID; }
+  if (!in->means3D || !in->opacities || !in->bg || !in->viewmatrix || !in->projmatrix || !in->campos) {
+    set_error("a required input pointer is NULL"); return GSR_ERR_INVALID;
+  }
+  if ((in->shs == nullptr) == (in->colors_precomp == nullptr)) {
+    set_error("Please provide excatly one of either SHs or precomputed colors!"); return GSR_ERR_INVALID;
+  }
+  const bool sr = in->scales != nullptr && in->rotations != nullptr;
+  if (sr == (in->cov3D_precomp != nullptr) || ((in->scales != nullptr) != (in->rotations != nullptr))) {
+    set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    return GSR_ERR_INVALID;
+  }
+  if (in->shs && (in->M < 1 || in->D < 0 || in->D > 3 || (in->D + 1) * (in->D + 1) > in->M)) {
+    set_error("SH degree %d needs %d coefficients, M=%d", in->D, (in->D + 1) * (in->D + 1), in->M); return GSR_ERR_INVALID;
+  }
+  if (in->K != 0 && (in->K != MAX_OBJ || !in->obj_feats)) { set_error("object channels: K must be 0 or 16 with obj_feats"); return GSR_ERR_INVALID; }
+  return GSR_OK;
+}
+
+static int debug_sync(const gsr_inputs* in, cudaStream_t st, const char* stage) {
+  if (!in->debug) return GSR_OK;
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { set_error("[CUDA ERROR] after %s: %s", stage, cudaGetErrorString(e)); return GSR_ERR_CUDA; }
+  return GSR_OK;
+}
+#define GSR_TRY(x) do { int _r = (x); if (_r != GSR_OK) return _r; } while (0)
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" {
+
+int gsr_abi_version(void) { return GSR_ABI_VERSION; }
+const char* gsr_last_error(void) { return g_err; }
+uint32_t gsr_higher_msb(uint32_t n) { return higher_msb(n); }
+
+size_t gsr_geom_bytes(int32_t P) { return Geom(nullptr, P).bytes; }
+size_t gsr_image_bytes(int32_t W, int32_t H) { return Image(nullptr, W, H).bytes; }
+size_t gsr_scratch_bytes(int32_t P, int64_t L_cap, int32_t, int32_t) { return Scratch(nullptr, P, L_cap).bytes; }
+size_t gsr_sort_temp_bytes(int64_t n) { return SortTemp(nullptr, n).bytes + align_up((size_t)n * 8) + align_up((size_t)n * 4); }
+
+int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void* scratch, size_t scratch_bytes,
+                         uint32_t* num_rendered_dev, uint32_t* num_rendered_host, void* stream) {
+  GSR_TRY(check_inputs(in));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!geom || !radii || !scratch || !num_rendered_dev) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  if (scratch_bytes < Scratch(nullptr, in->P, 0).bytes) { set_error("scratch too small"); return GSR_ERR_CAPACITY; }
+  if (in->P == 0) {
+    GSR_CUDA_CHECK(cudaMemsetAsync(num_rendered_dev, 0, 4, st));
+    if (num_rendered_host) *num_rendered_host = 0;
+    return GSR_OK;
+  }
+  Geom g(geom, in->P);
+  Scratch s(scratch, in->P, 0);
+  GSR_TRY(launch_preprocess_fwd(*in, g, radii, s, num_rendered_dev, st));
+  GSR_TRY(debug_sync(in, st, "preprocess"));
+  if (num_rendered_host)
+    GSR_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, 4, cudaMemcpyDeviceToHost, st));
+  if (in->prefiltered) {
+    uint32_t flag = 0;
+    GSR_CUDA_CHECK(cudaMemcpyAsync(&flag, s.flags, 4, cudaMemcpyDeviceToHost, st));
+    GSR_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (flag) { set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return GSR_ERR_PREFILTERED; }
+  }
+  return GSR_OK;
+}
+
+int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, uint32_t* point_list,
+                       void* image, void* scratch, size_t scratch_bytes, float* out_color, float* out_objects,
+                       void* stream) {
+  GSR_TRY(check_inputs(in));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!image || !out_color || (in->K > 0 && !out_objects) || L < 0) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  const size_t HW = (size_t)in->W * in->H;
+  if (in->P == 0) {  // rasterize_points.cu:68,81: zero-filled image, nothing launched
+    GSR_CUDA_CHECK(cudaMemsetAsync(out_color, 0, 3 * HW * sizeof(float), st));
+    if (in->K > 0) GSR_CUDA_CHECK(cudaMemsetAsync(out_objects, 0, in->K * HW * sizeof(float), st));
+    return GSR_OK;
+  }
+  if (!geom || !radii || !scratch || (L > 0 && !point_list)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  if (scratch_bytes < Scratch(nullptr, in->P, L).bytes) {
+    set_error("scratch too small: need %zu bytes for L=%lld", Scratch(nullptr, in->P, L).bytes, (long long)L);
+    return GSR_ERR_CAPACITY;
+  }
+  Geom g(const_cast<void*>(geom), in->P);
+  Image im(image, in->W, in->H);
+  Scratch s(scratch, in->P, L);
+  const int gx = (in->W + TILE_X - 1) / TILE_X, gy = (in->H + TILE_Y - 1) / TILE_Y;
+  const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));
+  const int passes = (end_bit + 7) / 8;
+  // pass p reads pair (p&1) and writes the other: start in the pair that makes the result land in
+  // (keys_b, point_list)
+  uint64_t* k0 = (passes & 1) ? s.keys_a : s.keys_b;
+  uint64_t* k1 = (passes & 1) ? s.keys_b : s.keys_a;
+  uint32_t* v0 = (passes & 1) ? s.vals_a : point_list;
+  uint32_t* v1 = (passes & 1) ? point_list : s.vals_a;
+  if (L > 0) {
+    GSR_TRY(launch_duplicate_keys(in->P, g, radii, gx, k0, v0, st));
+    GSR_TRY(debug_sync(in, st, "duplicate_keys"));
+    GSR_TRY(launch_sort_pairs_pingpong(k0, v0, k1, v1, L, end_bit, s.sort_temp, nullptr, st));
+    GSR_TRY(debug_sync(in, st, "sort"));
+  }
+  GSR_TRY(launch_tile_ranges(L, s.keys_b, im.ranges, gx * gy, st));
+  GSR_TRY(debug_sync(in, st, "tile_ranges"));
+  GSR_TRY(launch_blend_fwd(*in, g, im, point_list, out_color, out_objects, st));
+  GSR_TRY(debug_sync(in, st, "blend_fwd"));
+  return GSR_OK;
+}
+
+int gsr_backward(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, const uint32_t* point_list,
+                 const void* image, void* scratch, size_t scratch_bytes, const float* dL_dpix, const float* dL_dobjpix,
+                 float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dobj, void* stream) {
+  GSR_TRY(check_inputs(in));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (in->P == 0) return GSR_OK;
+  if (!geom || !radii || !image || !scratch || !dL_dpix || !dL_dmean2D || !dL_dopacity || !dL_dmean3D ||
+      (L > 0 && !point_list)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  if (in->shs && !dL_dsh) { set_error("dL_dsh is NULL but shs given"); return GSR_ERR_INVALID; }
+  if (in->scales && (!dL_dscale || !dL_drot)) { set_error("dL_dscale/dL_drot NULL but scales given"); return GSR_ERR_INVALID; }
+  if (in->cov3D_precomp && !dL_dcov3D) { set_error("dL_dcov3D NULL but cov3D_precomp given"); return GSR_ERR_INVALID; }
+  if (in->colors_precomp && !dL_dcolor) { set_error("dL_dcolor NULL but colors_precomp given"); return GSR_ERR_INVALID; }
+  if (in->K > 0 && (!dL_dobjpix || !dL_dobj)) { set_error("object gradients NULL but K>0"); return GSR_ERR_INVALID; }
+  if (scratch_bytes < Scratch(nullptr, in->P, 0).bytes) { set_error("scratch too small"); return GSR_ERR_CAPACITY; }
+  Geom g(const_cast<void*>(geom), in->P);
+  Image im(const_cast<void*>(image), in->W, in->H);
+  Scratch s(scratch, in->P, 0);
+  GSR_TRY(launch_blend_bwd(*in, g, im, point_list, dL_dpix, dL_dobjpix, s.accum, dL_dobj, st));
+  GSR_TRY(debug_sync(in, st, "blend_bwd"));
+  GSR_TRY(launch_preprocess_bwd(*in, g, radii, s.accum, dL_dmean2D, dL_dopacity, in->colors_precomp ? dL_dcolor : nullptr,
+                                dL_dmean3D, in->cov3D_precomp ? dL_dcov3D : nullptr, in->shs ? dL_dsh : nullptr,
+                                in->scales ? dL_dscale : nullptr, in->scales ? dL_drot : nullptr, st));
+  GSR_TRY(debug_sync(in, st, "preprocess_bwd"));
+  return GSR_OK;
+}
+
+int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* /*projmatrix*/,
+                     uint8_t* present, void* stream) {
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) { set_error("mark_visible: bad arguments"); return GSR_ERR_INVALID; }
+  if (P == 0) return GSR_OK;
+  return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+}
+
+int gsr_sort_pairs_u64(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                       int64_t n, int32_t end_bit, void* temp, size_t temp_bytes, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n < 0 || end_bit < 1 || end_bit > 64) { set_error("sort: bad n/end_bit"); return GSR_ERR_INVALID; }
+  if (n == 0) return GSR_OK;
+  if (temp_bytes < gsr_sort_temp_bytes(n)) { set_error("sort temp too small"); return GSR_ERR_CAPACITY; }
+  Carver c(temp);
+  void* st_temp = c.take<char>(SortTemp(nullptr, n).bytes);
+  uint64_t* ktmp = c.take<uint64_t>((size_t)n);
+  uint32_t* vtmp = c.take<uint32_t>((size_t)n);
+  const int passes = (end_bit + 7) / 8;
+  uint64_t* k0 = (passes & 1) ? ktmp : keys_out;
+  uint32_t* v0 = (passes & 1) ? vtmp : vals_out;
+  uint64_t* k1 = (passes & 1) ? keys_out : ktmp;
+  uint32_t* v1 = (passes & 1) ? vals_out : vtmp;
+  GSR_CUDA_CHECK(cudaMemcpyAsync(k0, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+  GSR_CUDA_CHECK(cudaMemcpyAsync(v0, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+  return launch_sort_pairs_pingpong(k0, v0, k1, v1, n, end_bit, st_temp, nullptr, st);
+}
+
+int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64_t L, const void* geom,
+                        const void* image, const void* scratch, void* dst, int64_t cap, void* stream) {
+  Geom g(const_cast<void*>(geom), P);
+  Image im(const_cast<void*>(image), W, H);
+  Scratch s(const_cast<void*>(scratch), P, L);
+  const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+  const int passes = (32 + (int)higher_msb((uint32_t)(gx * gy)) + 7) / 8;
+  const size_t n = (size_t)P, HW = (size_t)W * H;
+  const void* src = nullptr;
+  size_t bytes = 0;
+#define F(nm, ptr, cnt) if (!strcmp(name, nm)) { src = ptr; bytes = (cnt); }
+  F("depths", g.depths, n * 4) F("means2D", g.means2D, n * 8) F("cov3D", g.cov3D, n * 24)
+  F("conic_opacity", g.conic_opacity, n * 16) F("rgb", g.rgb_thr, n * 16) F("clamped", g.clamped, n)
+  F("tiles_touched", g.tiles_touched, n * 4) F("point_offsets", g.point_offsets, n * 4) F("rects", g.rects, n * 8)
+  F("final_T", im.final_T, HW * 4) F("n_contrib", im.n_contrib, HW * 4) F("ranges", im.ranges, (size_t)gx * gy * 8)
+  F("keys_sorted", s.keys_b, (size_t)L * 8)
+  // the unsorted pairs survive only when the pass count is odd (they are the ping-pong partner otherwise)
+  if (passes & 1) { F("keys_unsorted", s.keys_a, (size_t)L * 8) F("vals_unsorted", s.vals_a, (size_t)L * 4) }
+#undef F
+  if (!src) { set_error("debug_fetch: unknown or unavailable array '%s'", name); return GSR_ERR_INVALID; }
+  if (dst) {
+    const size_t ncopy = bytes < (size_t)cap ? bytes : (size_t)cap;
+    if (cudaMemcpyAsync(dst, src, ncopy, cudaMemcpyDeviceToDevice, (cudaStream_t)stream) != cudaSuccess) {
+      set_error("debug_fetch: copy failed"); return GSR_ERR_CUDA;
+    }
+  }
+  return (int64_t)bytes;
+}
+
+}  // extern "C"

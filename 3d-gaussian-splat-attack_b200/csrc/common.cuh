@@ -1,0 +1,167 @@
+// common.cuh -- shared declarations of the sm_100a rasterizer kernels (internal; the public
+// boundary is include/gsr_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/gsr_b200.h"
+
+namespace gsr {
+
+constexpr int TILE_X = 16;  // DGR/cuda_rasterizer/config.h:16-17 (BLOCK_X/BLOCK_Y); part of the result
+constexpr int TILE_Y = 16;  // definition: tile lists and n_contrib depend on it
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+constexpr int MAX_OBJ = 16;  // scene/gaussian_model.py:52 num_objects
+
+// ---- thread-local error string ------------------------------------------------------------
+void set_error(const char* fmt, ...);
+#define GSR_CUDA_CHECK(expr)                                                                   \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess) {                                                                   \
+      gsr::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return GSR_ERR_CUDA;                                                                     \
+    }                                                                                          \
+  } while (0)
+#define GSR_LAUNCH_CHECK(name)                                                                 \
+  do {                                                                                         \
+    cudaError_t _e = cudaGetLastError();                                                       \
+    if (_e != cudaSuccess) {                                                                   \
+      gsr::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));                 \
+      return GSR_ERR_CUDA;                                                                     \
+    }                                                                                          \
+  } while (0)
+
+// ---- buffer carving (all sub-arrays 256-byte aligned) ---------------------------------------
+inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+struct Carver {
+  char* base;
+  size_t off = 0;
+  explicit Carver(void* b) : base((char*)b) {}
+  template <typename T>
+  T* take(size_t n) {
+    T* p = (T*)(base ? base + off : nullptr);
+    off = align_up(off + n * sizeof(T));
+    return p;
+  }
+};
+
+// Per-view geometry state (what the reference keeps in GeometryState, rasterizer_impl.h:29-44,
+// minus CUB temp, plus the tile rect and the packed blend record).
+struct Geom {
+  float* depths;           // [P]
+  float2* means2D;         // [P]
+  float4* conic_opacity;   // [P]
+  float4* rgb_thr;         // [P]  (r, g, b, power threshold below which alpha < 1/255)
+  float* cov3D;            // [6P]
+  uint8_t* clamped;        // [P]  bit c set <=> channel c was clamped at 0 (forward.cu:66-69)
+  uint32_t* tiles_touched; // [P]
+  uint32_t* point_offsets; // [P]  inclusive prefix sum of tiles_touched
+  ushort4* rects;          // [P]  (x0, y0, x1, y1) tile rect (auxiliary.h:46-56)
+  size_t bytes;
+  Geom(void* buf, int P) {
+    Carver c(buf);
+    size_t n = (size_t)P;
+    depths = c.take<float>(n);
+    means2D = c.take<float2>(n);
+    conic_opacity = c.take<float4>(n);
+    rgb_thr = c.take<float4>(n);
+    cov3D = c.take<float>(6 * n);
+    clamped = c.take<uint8_t>(n);
+    tiles_touched = c.take<uint32_t>(n);
+    point_offsets = c.take<uint32_t>(n);
+    rects = c.take<ushort4>(n);
+    bytes = c.off;
+  }
+};
+
+// Per-view image state (ImageState, rasterizer_impl.h:46-53).
+struct Image {
+  float* final_T;       // [W*H]
+  uint32_t* n_contrib;  // [W*H]
+  uint2* ranges;        // [tiles]
+  size_t bytes;
+  Image(void* buf, int W, int H) {
+    Carver c(buf);
+    size_t n = (size_t)W * H;
+    size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    final_T = c.take<float>(n);
+    n_contrib = c.take<uint32_t>(n);
+    ranges = c.take<uint2>(tiles);
+    bytes = c.off;
+  }
+};
+
+// ---- radix sort geometry ---------------------------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 pairs per block
+constexpr int SORT_MAX_PASSES = 8;
+inline int64_t sort_tiles(int64_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }
+
+struct SortTemp {
+  uint32_t* hist;     // [SORT_MAX_PASSES][256] digit histograms -> exclusive offsets
+  uint32_t* tickets;  // [SORT_MAX_PASSES] dynamic tile ids
+  uint32_t* status;   // [SORT_MAX_PASSES][tiles][256] decoupled look-back words
+  size_t zero_bytes;  // prefix of the buffer that must be zeroed before a sort
+  size_t bytes;
+  SortTemp(void* buf, int64_t n) {
+    Carver c(buf);
+    hist = c.take<uint32_t>(SORT_MAX_PASSES * 256);
+    tickets = c.take<uint32_t>(64);
+    status = c.take<uint32_t>((size_t)SORT_MAX_PASSES * sort_tiles(n) * 256);
+    zero_bytes = c.off;
+    bytes = c.off;
+  }
+};
+
+// Reusable scratch (not needed after the call that used it returns).
+constexpr int PRE_THREADS = 256;  // Gaussians per preprocess block
+struct Scratch {
+  unsigned long long* scan_status;  // [pre_blocks] look-back words of the fused prefix sum
+  uint32_t* scan_ticket;            // [64]
+  uint32_t* flags;                  // [64] flags[0] = prefiltered violation
+  uint64_t* keys_a;                 // [L] unsorted keys
+  uint64_t* keys_b;                 // [L] sorted keys
+  uint32_t* vals_a;                 // [L] unsorted values
+  void* sort_temp;
+  float* accum;                     // [P][12] backward accumulators
+  size_t scan_zero_bytes;
+  size_t bytes;
+  Scratch(void* buf, int P, int64_t L) {
+    Carver c(buf);
+    size_t pre_blocks = ((size_t)P + PRE_THREADS - 1) / PRE_THREADS;
+    scan_status = c.take<unsigned long long>(pre_blocks + 1);
+    scan_ticket = c.take<uint32_t>(64);
+    flags = c.take<uint32_t>(64);
+    scan_zero_bytes = c.off;
+    accum = c.take<float>((size_t)P * 12);
+    keys_a = c.take<uint64_t>((size_t)L);
+    keys_b = c.take<uint64_t>((size_t)L);
+    vals_a = c.take<uint32_t>((size_t)L);
+    sort_temp = c.take<char>(SortTemp(nullptr, L).bytes);
+    bytes = c.off;
+  }
+};
+
+// ---- stage launchers (each returns a gsr_status) ---------------------------------------------
+int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch& s, uint32_t* num_rendered_dev,
+                          cudaStream_t st);
+int launch_duplicate_keys(int P, const Geom& g, const int32_t* radii, int gx, uint64_t* keys, uint32_t* vals,
+                          cudaStream_t st);
+int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
+                               int end_bit, void* temp, int* passes_out, cudaStream_t st);
+int launch_tile_ranges(int64_t L, const uint64_t* keys_sorted, uint2* ranges, int tiles, cudaStream_t st);
+int launch_blend_fwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
+                     float* out_color, float* out_objects, cudaStream_t st);
+int launch_blend_bwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
+                     const float* dL_dpix, const float* dL_dobjpix, float* accum, float* dL_dobj, cudaStream_t st);
+int launch_preprocess_bwd(const gsr_inputs& in, const Geom& g, const int32_t* radii, const float* accum,
+                          float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
+                          float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, cudaStream_t st);
+int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
+
+uint32_t higher_msb(uint32_t n);
+
+}  // namespace gsr

@@ -1,0 +1,212 @@
+// radix_sort.cu -- hand-written stable onesweep LSD radix sort of (u64 key, u32 value) pairs.
+//
+// Replaces cub::DeviceRadixSort::SortPairs (DGR/cuda_rasterizer/rasterizer_impl.cu:303-308):
+// ascending, stable, on key bits [0, end_bit).  No CUB / Thrust.
+//
+//   1. one histogram kernel reads the keys once and builds the 256-bin digit histogram of every
+//      pass (shared-memory atomics, then one global atomic per bin per block);
+//   2. a one-block kernel turns each histogram into exclusive digit offsets;
+//   3. one scatter kernel per 8-bit digit: each block takes a 4096-pair tile (dynamic ticket),
+//      ranks its keys with warp-level __match_any_sync multi-split into per-warp shared-memory
+//      digit counters (stable: item order inside a warp is preserved), chains tile prefixes with a
+//      decoupled look-back over per-digit status words, stages the tile in shared memory in
+//      sorted order and writes it out in coalesced per-digit runs.
+// HBM traffic: 8 B/pair (histogram) + 24 B/pair/pass.
+#include "common.cuh"
+
+namespace gsr {
+namespace {
+
+constexpr uint32_t ST_AGG = 1u << 30, ST_PREFIX = 1u << 31, ST_MASK = (1u << 30) - 1;
+constexpr int NWARPS = SORT_THREADS / 32;
+
+__global__ void __launch_bounds__(256)
+sort_histogram_kernel(const uint64_t* __restrict__ keys, int64_t n, int passes, int end_bit,
+                      uint32_t* __restrict__ hist) {
+  __shared__ uint32_t sh[SORT_MAX_PASSES * 256];
+  for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint64_t k = keys[i];
+    for (int p = 0; p < passes; p++) {
+      const int shift = 8 * p, nb = min(8, end_bit - shift);
+      atomicAdd(&sh[p * 256 + (uint32_t)((k >> shift) & ((1u << nb) - 1))], 1u);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < passes * 256; i += blockDim.x)
+    if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
+// exclusive scan of each pass's 256 bins, in place; one warp per pass
+__global__ void sort_scan_hist_kernel(uint32_t* hist, int passes) {
+  const int p = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (p >= passes) return;
+  uint32_t* h = hist + p * 256;
+  uint32_t v[8], sum = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) { v[k] = h[lane * 8 + k]; sum += v[k]; }
+  uint32_t incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  uint32_t run = incl - sum;
+#pragma unroll
+  for (int k = 0; k < 8; k++) { h[lane * 8 + k] = run; run += v[k]; }
+}
+
+struct PassSmem {
+  uint64_t keys[SORT_TILE];
+  uint32_t vals[SORT_TILE];
+  uint32_t warp_hist[NWARPS][256];
+  uint32_t digit_off[256];   // exclusive offset of each digit inside the sorted tile
+  int32_t global_base[256];  // destination of sorted tile slot s with digit d is global_base[d] + s
+  uint32_t scan_tmp[NWARPS];
+  uint32_t tile;
+};
+
+__global__ void __launch_bounds__(SORT_THREADS)
+onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
+                     const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, int64_t n, int shift,
+                     uint32_t digit_mask, const uint32_t* __restrict__ digit_base, uint32_t* status,
+                     uint32_t* ticket) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  PassSmem& S = *reinterpret_cast<PassSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) S.tile = atomicAdd(ticket, 1u);
+#pragma unroll
+  for (int w = 0; w < NWARPS; w++) S.warp_hist[w][tid] = 0;
+  __syncthreads();
+  const uint32_t tile = S.tile;
+  const int64_t tile_base = (int64_t)tile * SORT_TILE;
+  const int tile_n = (int)min((int64_t)SORT_TILE, n - tile_base);
+
+  // warp-striped load: warp w owns tile items [w*512, (w+1)*512), lane-interleaved
+  uint64_t key[SORT_ITEMS];
+  uint32_t val[SORT_ITEMS], rank[SORT_ITEMS];
+  const int wbase = warp * (32 * SORT_ITEMS) + lane;
+#pragma unroll
+  for (int i = 0; i < SORT_ITEMS; i++) {
+    const int t = wbase + i * 32;
+    if (t < tile_n) { key[i] = keys_in[tile_base + t]; val[i] = vals_in[tile_base + t]; }
+    else { key[i] = ~0ull; val[i] = 0; }
+  }
+
+  // stable per-warp ranking
+  uint32_t* wh = S.warp_hist[warp];
+  const uint32_t lt_mask = (1u << lane) - 1;
+#pragma unroll
+  for (int i = 0; i < SORT_ITEMS; i++) {
+    const bool valid = wbase + i * 32 < tile_n;
+    const uint32_t d = valid ? (uint32_t)(key[i] >> shift) & digit_mask : 0xffffffffu;
+    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t pre = 0;
+    if (valid && lane == leader) { pre = wh[d]; wh[d] = pre + __popc(peers); }
+    pre = __shfl_sync(0xffffffffu, pre, leader);
+    rank[i] = pre + __popc(peers & lt_mask);
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // thread t owns digit t: prefix over warps, publish the tile aggregate, look back
+  uint32_t count = 0;
+#pragma unroll
+  for (int w = 0; w < NWARPS; w++) {
+    const uint32_t c = S.warp_hist[w][tid];
+    S.warp_hist[w][tid] = count;
+    count += c;
+  }
+  volatile uint32_t* st = status;
+  if (tile == 0) st[tid] = ST_PREFIX | count;
+  else st[(size_t)tile * 256 + tid] = ST_AGG | count;
+  // exclusive scan of `count` over the 256 digits
+  uint32_t incl = count;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) S.scan_tmp[warp] = incl;
+  __syncthreads();
+  uint32_t wpre = 0;
+#pragma unroll
+  for (int w = 0; w < NWARPS; w++) wpre += w < warp ? S.scan_tmp[w] : 0u;
+  const uint32_t doff = wpre + incl - count;
+  S.digit_off[tid] = doff;
+  uint32_t excl = 0;
+  if (tile != 0) {
+    __threadfence();
+    int64_t j = (int64_t)tile - 1;
+    while (true) {
+      const uint32_t w = st[(size_t)j * 256 + tid];
+      if ((w & (ST_AGG | ST_PREFIX)) == 0) continue;
+      excl += w & ST_MASK;
+      if (w & ST_PREFIX) break;
+      j--;
+    }
+    st[(size_t)tile * 256 + tid] = ST_PREFIX | ((excl + count) & ST_MASK);
+  }
+  S.global_base[tid] = (int32_t)(digit_base[tid] + excl) - (int32_t)doff;
+  __syncthreads();
+
+  // stage in sorted order
+#pragma unroll
+  for (int i = 0; i < SORT_ITEMS; i++) {
+    if (wbase + i * 32 < tile_n) {
+      const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
+      const uint32_t pos = S.digit_off[d] + wh[d] + rank[i];
+      S.keys[pos] = key[i];
+      S.vals[pos] = val[i];
+    }
+  }
+  __syncthreads();
+  // coalesced per-digit runs
+  for (int s = tid; s < tile_n; s += SORT_THREADS) {
+    const uint64_t k = S.keys[s];
+    const uint32_t d = (uint32_t)(k >> shift) & digit_mask;
+    const int64_t dst = (int64_t)(uint32_t)(S.global_base[d] + s);
+    keys_out[dst] = k;
+    vals_out[dst] = S.vals[s];
+  }
+}
+
+}  // namespace
+
+// Sorts in place across two buffer pairs: pass p reads pair (p & 1) and writes the other; the
+// result is in pair (passes & 1).  Returns the pass count through *passes_out.
+int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
+                               int end_bit, void* temp, int* passes_out, cudaStream_t st) {
+  const int passes = (end_bit + 7) / 8;
+  if (passes_out) *passes_out = passes;
+  if (passes < 1 || passes > SORT_MAX_PASSES) { set_error("sort: end_bit %d out of range", end_bit); return GSR_ERR_INVALID; }
+  if (n >= (int64_t)ST_MASK) { set_error("sort: %lld pairs exceed the 2^30 limit", (long long)n); return GSR_ERR_INVALID; }
+  if (n == 0) return GSR_OK;
+  SortTemp T(temp, n);
+  GSR_CUDA_CHECK(cudaMemsetAsync(temp, 0, T.zero_bytes, st));
+  const int hist_blocks = (int)min((int64_t)148 * 8, (n + 2047) / 2048);
+  sort_histogram_kernel<<<hist_blocks, 256, 0, st>>>(keys0, n, passes, end_bit, T.hist);
+  GSR_LAUNCH_CHECK("sort_histogram_kernel");
+  sort_scan_hist_kernel<<<1, 32 * SORT_MAX_PASSES, 0, st>>>(T.hist, passes);
+  GSR_LAUNCH_CHECK("sort_scan_hist_kernel");
+  GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(PassSmem)));
+  const int64_t tiles = sort_tiles(n);
+  for (int p = 0; p < passes; p++) {
+    const int shift = 8 * p, nb = end_bit - shift < 8 ? end_bit - shift : 8;
+    const uint64_t* kin = (p & 1) ? keys1 : keys0;
+    uint64_t* kout = (p & 1) ? keys0 : keys1;
+    const uint32_t* vin = (p & 1) ? vals1 : vals0;
+    uint32_t* vout = (p & 1) ? vals0 : vals1;
+    onesweep_pass_kernel<<<(unsigned)tiles, SORT_THREADS, sizeof(PassSmem), st>>>(
+        kin, kout, vin, vout, n, shift, (1u << nb) - 1, T.hist + p * 256, T.status + (size_t)p * tiles * 256,
+        T.tickets + p);
+    GSR_LAUNCH_CHECK("onesweep_pass_kernel");
+  }
+  return GSR_OK;
+}
+
+}  // namespace gsr

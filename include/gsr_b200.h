@@ -1,0 +1,129 @@
+/* gsr_b200.h -- C ABI of the B200-native differentiable Gaussian-splat rasterizer.
+ *
+ * This is the drop-in boundary for the hot path of poloclub/3d-gaussian-splat-attack:
+ * it replaces the private pybind module `diff_gaussian_rasterization._C`
+ *   (DGR/ext.cpp:15-19, DGR/rasterize_points.h:18-67;
+ *    DGR = submodules/gaussian-splatting/submodules/diff-gaussian-rasterization)
+ * and the C++ class behind it, CudaRasterizer::Rasterizer (DGR/cuda_rasterizer/rasterizer.h:20-85).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes, no torch types.  Every pointer named in gsr_inputs and
+ *    every buffer argument is a DEVICE pointer unless the name ends in _host.
+ *  - NULL pointer = absent input (the reference passes empty tensors -> nullptr,
+ *    DGR/diff_gaussian_rasterization/__init__.py:197-207, forward.cu:205,241).
+ *  - The caller owns every buffer; the library never allocates device memory.  Buffer sizes come
+ *    from the gsr_*_bytes() queries.  All buffers must be 256-byte aligned.
+ *  - Every launch goes to the cudaStream_t passed in (as void*); the reference uses the legacy
+ *    default stream.
+ *  - Every entry point returns 0 on success or a negative gsr_status; gsr_last_error() returns
+ *    a message for the last failure on the calling thread.
+ */
+#ifndef GSR_B200_H
+#define GSR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_ABI_VERSION 1
+
+typedef enum {
+  GSR_OK = 0,
+  GSR_ERR_INVALID = -1,   /* bad argument (shape / NULL / exclusivity)                         */
+  GSR_ERR_CUDA = -2,      /* a CUDA runtime call or launch failed                              */
+  GSR_ERR_CAPACITY = -3,  /* a caller buffer is too small (needed size reported by the call)   */
+  GSR_ERR_PREFILTERED = -4 /* prefiltered=1 but a Gaussian was culled (auxiliary.h:156-160)    */
+} gsr_status;
+
+/* Inputs of one view; mirrors the argument list of Rasterizer::forward
+ * (DGR/cuda_rasterizer/rasterizer.h:27-50) plus the optional object-feature channel that
+ * gaussian_renderer/__init__.py:86-95 passes as sh_objs. */
+typedef struct gsr_inputs {
+  int32_t P;              /* number of Gaussians                                            */
+  int32_t D;              /* active SH degree (0..3)                                        */
+  int32_t M;              /* SH coefficients per Gaussian in `shs` ((max_degree+1)^2), 0 if none */
+  int32_t W, H;           /* image size                                                     */
+  int32_t K;              /* object-feature channels (0 = none, <= 16)                      */
+  int32_t prefiltered;    /* reference flag: trap if a Gaussian is near-culled              */
+  int32_t debug;          /* reference flag: synchronise + check after every stage          */
+  float scale_modifier, tanfovx, tanfovy;
+  float _pad;
+  const float* bg;             /* (>=3)                                                     */
+  const float* means3D;        /* (P,3)                                                     */
+  const float* shs;            /* (P,M,3) or NULL                                           */
+  const float* colors_precomp; /* (P,3) or NULL                                             */
+  const float* opacities;      /* (P,1)                                                     */
+  const float* scales;         /* (P,3) or NULL                                             */
+  const float* rotations;      /* (P,4) or NULL                                             */
+  const float* cov3D_precomp;  /* (P,6) or NULL                                             */
+  const float* viewmatrix;     /* (4,4) column-major in memory (scene/cameras.py:54)        */
+  const float* projmatrix;     /* (4,4) column-major in memory                              */
+  const float* campos;         /* (3)                                                       */
+  const float* obj_feats;      /* (P,K) or NULL                                             */
+} gsr_inputs;
+
+int gsr_abi_version(void);
+const char* gsr_last_error(void);
+
+/* ---- buffer sizing (replaces required<GeometryState/ImageState/BinningState>,
+ *      DGR/cuda_rasterizer/rasterizer_impl.h:67-72) ---- */
+size_t gsr_geom_bytes(int32_t P);               /* per-view, kept until that view's backward   */
+size_t gsr_image_bytes(int32_t W, int32_t H);   /* per-view, kept until backward               */
+size_t gsr_scratch_bytes(int32_t P, int64_t L_cap, int32_t W, int32_t H);  /* reusable across views */
+
+/* ---- forward, phase 1: preprocess + fused prefix sum (forward.cu:155-256 preprocessCUDA,
+ *      rasterizer_impl.cu:277 InclusiveSum).  Writes radii (P) and the geometry buffer, and the
+ *      number of (tile, Gaussian) duplicates L to *num_rendered_dev (device u32); when
+ *      num_rendered_host (pinned) is non-NULL it is also copied there asynchronously. ---- */
+int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void* scratch, size_t scratch_bytes,
+                         uint32_t* num_rendered_dev, uint32_t* num_rendered_host, void* stream);
+
+/* ---- forward, phase 2: duplicateWithKeys + radix sort + identifyTileRanges + blending
+ *      (rasterizer_impl.cu:289-334, forward.cu:261-374).  L must be the value produced by phase 1.
+ *      point_list (L u32) is an output kept for backward.  out_color (3,H,W); out_objects (K,H,W)
+ *      when in->K > 0. ---- */
+int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
+                       uint32_t* point_list, void* image, void* scratch, size_t scratch_bytes,
+                       float* out_color, float* out_objects, void* stream);
+
+/* ---- backward (Rasterizer::backward, rasterizer_impl.cu:340-433; rasterize_points.cu:117-196).
+ *      All gradient outputs are fully written (no pre-zeroing by the caller).  Pass NULL for
+ *      dL_dsh / dL_dscale+dL_drot / dL_dcov3D / dL_dcolor when the matching input is absent.
+ *      dL_dcov3D is written only when cov3D_precomp was given, dL_dcolor only when colors_precomp
+ *      was given (otherwise they are internal). ---- */
+int gsr_backward(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
+                 const uint32_t* point_list, const void* image, void* scratch, size_t scratch_bytes,
+                 const float* dL_dpix, const float* dL_dobjpix,
+                 float* dL_dmean2D /*(P,3)*/, float* dL_dopacity /*(P,1)*/, float* dL_dcolor /*(P,3)*/,
+                 float* dL_dmean3D /*(P,3)*/, float* dL_dcov3D /*(P,6)*/, float* dL_dsh /*(P,M,3)*/,
+                 float* dL_dscale /*(P,3)*/, float* dL_drot /*(P,4)*/, float* dL_dobj /*(P,K)*/, void* stream);
+
+/* ---- markVisible (rasterizer_impl.cu:141-153, checkFrustum :54-66); present is (P) bytes ---- */
+int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/* ---- stage-level entry points (parity tests and per-stage roofline timing) ---- */
+
+/* Stable LSD radix sort of (u64 key, u32 value) pairs on bits [0, end_bit); replaces
+ * cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:303-308). temp >= gsr_sort_temp_bytes(n). */
+size_t gsr_sort_temp_bytes(int64_t n);
+int gsr_sort_pairs_u64(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                       int64_t n, int32_t end_bit, void* temp, size_t temp_bytes, void* stream);
+
+/* Copies internal arrays of a finished forward out for inspection. name is one of: "depths",
+ * "means2D", "cov3D", "conic_opacity", "rgb", "clamped", "tiles_touched", "point_offsets", "rects",
+ * "final_T", "n_contrib", "ranges", "keys_unsorted", "vals_unsorted", "keys_sorted".
+ * Returns the byte count (copying min(count, cap) bytes into dst, a device pointer), <0 on error. */
+int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64_t L, const void* geom,
+                        const void* image, const void* scratch, void* dst, int64_t cap, void* stream);
+
+/* Host helper: number of key bits the tile id needs (getHigherMsb, rasterizer_impl.cu:35-50). */
+uint32_t gsr_higher_msb(uint32_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_B200_H */
