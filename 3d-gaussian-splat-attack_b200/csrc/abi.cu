@@ -19,6 +19,27 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+// ---- profiling state (process-wide; guarded by the caller's GIL / single host thread) ----------
+static bool g_prof_on = false;
+static long long g_launches = 0;
+struct ProfRec { int stage; cudaEvent_t a, b; };
+static ProfRec g_prof[8192];
+static int g_prof_n = 0, g_prof_made = 0;
+
+void count_launches(int n) { g_launches += n; }
+void profile_begin(int stage, cudaStream_t st) {
+  if (!g_prof_on || g_prof_n >= 8192) return;
+  ProfRec& r = g_prof[g_prof_n];
+  if (g_prof_n >= g_prof_made) { cudaEventCreate(&r.a); cudaEventCreate(&r.b); g_prof_made++; }
+  r.stage = stage;
+  cudaEventRecord(r.a, st);
+}
+void profile_end(int stage, cudaStream_t st) {
+  if (!g_prof_on || g_prof_n >= 8192) return;
+  cudaEventRecord(g_prof[g_prof_n].b, st);
+  g_prof_n++;
+}
+
 static int check_inputs(const gsr_inputs* in) {
   if (!in) { set_error("inputs is NULL"); return GSR_ERR_INVALID; }
   if (in->P < 0 || in->W <= 0 || in->H <= 0) { set_error("bad sizes P=%d W=%d H=%d", in->P, in->W, in->H); return GSR_ERR_INVALID; }
@@ -59,6 +80,21 @@ int gsr_abi_version(void) { return GSR_ABI_VERSION; }
 const char* gsr_last_error(void) { return g_err; }
 uint32_t gsr_higher_msb(uint32_t n) { return higher_msb(n); }
 
+int gsr_profile_enable(int on) { g_prof_on = on != 0; g_prof_n = 0; return GSR_OK; }
+int64_t gsr_launch_count(int reset) { long long v = g_launches; if (reset) g_launches = 0; return v; }
+int gsr_profile_read(float* ms_host, int32_t* calls_host) {
+  for (int i = 0; i < ST_COUNT; i++) { ms_host[i] = 0.f; if (calls_host) calls_host[i] = 0; }
+  for (int i = 0; i < g_prof_n; i++) {
+    float ms = 0.f;
+    GSR_CUDA_CHECK(cudaEventSynchronize(g_prof[i].b));
+    GSR_CUDA_CHECK(cudaEventElapsedTime(&ms, g_prof[i].a, g_prof[i].b));
+    ms_host[g_prof[i].stage] += ms;
+    if (calls_host) calls_host[g_prof[i].stage]++;
+  }
+  g_prof_n = 0;
+  return GSR_OK;
+}
+
 size_t gsr_geom_bytes(int32_t P) { return Geom(nullptr, P).bytes; }
 size_t gsr_image_bytes(int32_t W, int32_t H) { return Image(nullptr, W, H).bytes; }
 size_t gsr_scratch_bytes(int32_t P, int64_t L_cap, int32_t, int32_t) { return Scratch(nullptr, P, L_cap).bytes; }
@@ -77,7 +113,7 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   }
   Geom g(geom, in->P);
   Scratch s(scratch, in->P, 0);
-  GSR_TRY(launch_preprocess_fwd(*in, g, radii, s, num_rendered_dev, st));
+  { StageScope ps(ST_PREPROCESS_FWD, st); GSR_TRY(launch_preprocess_fwd(*in, g, radii, s, num_rendered_dev, st)); }
   GSR_TRY(debug_sync(in, st, "preprocess"));
   if (num_rendered_host)
     GSR_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, 4, cudaMemcpyDeviceToHost, st));
@@ -120,14 +156,14 @@ int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* ra
   uint32_t* v0 = (passes & 1) ? s.vals_a : point_list;
   uint32_t* v1 = (passes & 1) ? point_list : s.vals_a;
   if (L > 0) {
-    GSR_TRY(launch_duplicate_keys(in->P, g, radii, gx, k0, v0, st));
+    { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_duplicate_keys(in->P, g, radii, gx, k0, v0, st)); }
     GSR_TRY(debug_sync(in, st, "duplicate_keys"));
-    GSR_TRY(launch_sort_pairs_pingpong(k0, v0, k1, v1, L, end_bit, s.sort_temp, nullptr, st));
+    { StageScope ps(ST_SORT, st); GSR_TRY(launch_sort_pairs_pingpong(k0, v0, k1, v1, L, end_bit, s.sort_temp, nullptr, st)); }
     GSR_TRY(debug_sync(in, st, "sort"));
   }
-  GSR_TRY(launch_tile_ranges(L, s.keys_b, im.ranges, gx * gy, st));
+  { StageScope ps(ST_RANGES, st); GSR_TRY(launch_tile_ranges(L, s.keys_b, im.ranges, gx * gy, st)); }
   GSR_TRY(debug_sync(in, st, "tile_ranges"));
-  GSR_TRY(launch_blend_fwd(*in, g, im, point_list, out_color, out_objects, st));
+  { StageScope ps(ST_BLEND_FWD, st); GSR_TRY(launch_blend_fwd(*in, g, im, point_list, out_color, out_objects, st)); }
   GSR_TRY(debug_sync(in, st, "blend_fwd"));
   return GSR_OK;
 }
@@ -150,11 +186,12 @@ int gsr_backward(const gsr_inputs* in, const void* geom, const int32_t* radii, i
   Geom g(const_cast<void*>(geom), in->P);
   Image im(const_cast<void*>(image), in->W, in->H);
   Scratch s(scratch, in->P, 0);
-  GSR_TRY(launch_blend_bwd(*in, g, im, point_list, dL_dpix, dL_dobjpix, s.accum, dL_dobj, st));
+  { StageScope ps(ST_BLEND_BWD, st); GSR_TRY(launch_blend_bwd(*in, g, im, point_list, dL_dpix, dL_dobjpix, s.accum, dL_dobj, st)); }
   GSR_TRY(debug_sync(in, st, "blend_bwd"));
-  GSR_TRY(launch_preprocess_bwd(*in, g, radii, s.accum, dL_dmean2D, dL_dopacity, in->colors_precomp ? dL_dcolor : nullptr,
-                                dL_dmean3D, in->cov3D_precomp ? dL_dcov3D : nullptr, in->shs ? dL_dsh : nullptr,
-                                in->scales ? dL_dscale : nullptr, in->scales ? dL_drot : nullptr, st));
+  { StageScope ps(ST_PREPROCESS_BWD, st);
+    GSR_TRY(launch_preprocess_bwd(*in, g, radii, s.accum, dL_dmean2D, dL_dopacity, in->colors_precomp ? dL_dcolor : nullptr,
+                                  dL_dmean3D, in->cov3D_precomp ? dL_dcov3D : nullptr, in->shs ? dL_dsh : nullptr,
+                                  in->scales ? dL_dscale : nullptr, in->scales ? dL_drot : nullptr, st)); }
   GSR_TRY(debug_sync(in, st, "preprocess_bwd"));
   return GSR_OK;
 }

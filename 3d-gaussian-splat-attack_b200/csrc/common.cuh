@@ -15,6 +15,7 @@ constexpr int MAX_OBJ = 16;  // scene/gaussian_model.py:52 num_objects
 
 // ---- thread-local error string ------------------------------------------------------------
 void set_error(const char* fmt, ...);
+void count_launches(int n);
 #define GSR_CUDA_CHECK(expr)                                                                   \
   do {                                                                                         \
     cudaError_t _e = (expr);                                                                   \
@@ -26,6 +27,7 @@ void set_error(const char* fmt, ...);
 #define GSR_LAUNCH_CHECK(name)                                                                 \
   do {                                                                                         \
     cudaError_t _e = cudaGetLastError();                                                       \
+    gsr::count_launches(1);                                                                    \
     if (_e != cudaSuccess) {                                                                   \
       gsr::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));                 \
       return GSR_ERR_CUDA;                                                                     \
@@ -163,5 +165,18 @@ int launch_preprocess_bwd(const gsr_inputs& in, const Geom& g, const int32_t* ra
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 
 uint32_t higher_msb(uint32_t n);
+
+// ---- per-stage profiling (gsr_profile_*): CUDA events on the launching stream around each stage,
+// and a count of kernel launches (gsr_launch_count) ------------------------------------------------
+enum Stage { ST_PREPROCESS_FWD = 0, ST_DUPLICATE, ST_SORT, ST_RANGES, ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD,
+             ST_COUNT };
+void profile_begin(int stage, cudaStream_t st);
+void profile_end(int stage, cudaStream_t st);
+void count_launches(int n);
+struct StageScope {
+  int stage; cudaStream_t st;
+  StageScope(int s, cudaStream_t t) : stage(s), st(t) { profile_begin(stage, st); }
+  ~StageScope() { profile_end(stage, st); }
+};
 
 }  // namespace gsr

@@ -46,10 +46,14 @@ EXPORTS = {
     "gsr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_sort_pairs_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),
+    "gsr_profile_enable": (C.c_int, [C.c_int]),
+    "gsr_profile_read": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "gsr_launch_count": (C.c_int64, [C.c_int]),
     "gsr_debug_fetch": (C.c_int64, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
 }
 
+STAGES = ("preprocess_fwd", "duplicate_keys", "sort", "tile_ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")
 _lib = None
 
 

@@ -1,0 +1,422 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd views/sec of the B200-native Gaussian-splat rasterizer (BASELINE.json metric).
+
+A "step" is one DAGGER-style PGD gradient step on one rank: `--views` camera views (default 8,
+config C3's 64 views / 8 GPUs) are rendered forward and backward against a replicated Gaussian
+set (config C2: 1M Gaussians, SH degree 3, 1920x1080), attribute gradients accumulate over the
+views and -- for N > 1 -- are summed with one NCCL all-reduce.  views/sec = N * views * K / t.
+
+  value     inputs resident in HBM, public Python API (GaussianRasterizer + autograd backward)
+  e2e       same step driven from HOST buffers: Gaussian attributes, camera matrices and dL/dpixel
+            copied from pinned host memory every step, gradients read back to the host
+  roofline  dominant kernel, timed live with CUDA events on the launching stream (gsr_profile_*)
+  cpu_baseline / --impl reference: the CPU oracle (oracle/cpu_ref.cpp, OpenMP, all host cores) on
+            a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "3d-gaussian-splat-attack_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "fwd+bwd views/sec at 1080p, 1M Gaussians"
+UNIT = "views/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="gsr", choices=["gsr", "reference"])
+    ap.add_argument("--workload", default="C2", help="scene config of gsr_synth (C2 = BASELINE configs[1])")
+    ap.add_argument("--views", type=int, default=8, help="camera views per rank per step")
+    ap.add_argument("--P", type=int, default=None, help="override Gaussian count (debug)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-views", type=int, default=1)
+    ap.add_argument("--stages-out", default=None, help="write the per-stage table as JSON to this file")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback", 1965.0
+
+
+def cameras_for(scene, n_total):
+    from gsr_synth import ring_cameras
+    c = scene["cam"]
+    return ring_cameras(n_total, radius=3.0, width=c["image_width"], height=c["image_height"])
+
+
+# ------------------------------------------------------------------ CPU arm (oracle = checker, timed as baseline)
+def cpu_views_per_sec(scene, cams, steps, warmup, views):
+    """Times the CPU oracle (the reference's rasterizer math restated for the host, oracle/cpu_ref.cpp;
+    the reference has no CPU implementation of its own) on `views` views per step."""
+    from oracle.cpu_ref import Oracle, num_threads
+    cores = num_threads()
+    dL = scene["dL_dpix"]
+
+    def one(cam):
+        o = Oracle()
+        o.forward(scene["bg"], scene["means3D"], scene["opacities"], cam["viewmatrix"], cam["projmatrix"],
+                  cam["campos"], cam["image_width"], cam["image_height"], cam["tanfovx"], cam["tanfovy"],
+                  sh_degree=scene["sh_degree"], shs=scene["shs"], scales=scene["scales"], rotations=scene["rotations"])
+        o.backward(dL)
+
+    for i in range(warmup):
+        one(cams[i % len(cams)])
+    t0 = time.perf_counter()
+    n = 0
+    for s in range(steps):
+        for v in range(views):
+            one(cams[(s * views + v) % len(cams)])
+            n += 1
+    dt = time.perf_counter() - t0
+    return n / dt, dt, cores, n
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from gsr_synth import make_scene
+    scene = make_scene(args.workload, P=args.P)
+    cams = cameras_for(scene, max(args.views * args.gpus, 1))
+    steps, warmup = max(1, min(args.steps, 3)), min(args.warmup, 1)
+    vps, dt, cores, n = cpu_views_per_sec(scene, cams, steps, warmup, args.cpu_sample_views)
+    c = scene["cam"]
+    sample = f"{n} full view(s) fwd+bwd of {args.workload} (P={scene['P']}, {c['image_width']}x{c['image_height']}), {warmup} warm-up"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": vps, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {scene['P']} Gaussians SH3, {c['image_width']}x{c['image_height']}, fwd+bwd",
+                   "views_per_step": args.cpu_sample_views, "note": "reference has no CPU rasterizer; this is the CPU "
+                   "restatement of its CUDA math (oracle/cpu_ref.cpp) on all host cores"},
+        "cpu_baseline": {"value": vps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": vps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ GPU arm
+ATTRS = (("means3D", 3), ("shs", 48), ("scales", 3), ("rotations", 4), ("opacities", 1))  # floats per Gaussian
+SHAPES = {"means3D": (-1, 3), "shs": (-1, 16, 3), "scales": (-1, 3), "rotations": (-1, 4), "opacities": (-1, 1)}
+
+
+class Workload:
+    """Replicated Gaussian set in one flat HBM buffer (+ flat gradient buffer = the all-reduce bucket),
+    this rank's cameras and dL/dpixel images; pinned host mirrors for the e2e path."""
+
+    def __init__(self, args, torch, rank, world, dev):
+        from gsr_synth import make_scene
+        import diff_gaussian_rasterization as dgr
+        self.torch, self.dgr, self.dev, self.rank, self.world = torch, dgr, dev, rank, world
+        sc = self.scene = make_scene(args.workload, P=args.P)
+        self.P, self.W, self.H = sc["P"], sc["cam"]["image_width"], sc["cam"]["image_height"]
+        self.cams = cameras_for(sc, args.views * world)[rank::world]
+        host = np.concatenate([sc[n].reshape(-1) for n, _ in ATTRS]).astype(np.float32)
+        self.host_param = torch.from_numpy(host).pin_memory()
+        self.host_grad = torch.empty_like(self.host_param).pin_memory()
+        self.flat_param = self.host_param.to(dev)
+        self.flat_grad = torch.zeros_like(self.flat_param)
+        self.params, off = {}, 0
+        for n, k in ATTRS:
+            sz = self.P * k
+            p = self.flat_param[off:off + sz].view(SHAPES[n]).detach().requires_grad_(True)
+            p.grad = self.flat_grad[off:off + sz].view(SHAPES[n])
+            self.params[n] = p
+            off += sz
+        self.means2D = torch.zeros((self.P, 3), device=dev)  # dummy screen-space tensor (no grad wanted)
+        rng = np.random.default_rng(99 + rank)
+        nv = len(self.cams)
+        g = (rng.standard_normal((nv, 3, self.H, self.W), dtype=np.float32) / (3.0 * self.H * self.W))
+        self.host_dL = torch.from_numpy(g).pin_memory()
+        self.dev_dL = self.host_dL.to(dev)
+        cam_host = np.stack([np.concatenate([c["viewmatrix"].reshape(-1), c["projmatrix"].reshape(-1), c["campos"],
+                                             np.zeros(1, np.float32)]) for c in self.cams]).astype(np.float32)
+        self.host_cam = torch.from_numpy(cam_host).pin_memory()       # (nv, 36)
+        self.dev_cam = self.host_cam.to(dev)
+        self.bg = torch.zeros(3, device=dev)
+        self.h2d_bytes = self.host_param.numel() * 4 + self.host_dL.numel() * 4 + self.host_cam.numel() * 4
+        self.d2h_bytes = self.host_grad.numel() * 4
+        self.last_fn = None
+
+    def settings(self, v):
+        c, cm = self.cams[v], self.dev_cam[v]
+        return self.dgr.GaussianRasterizationSettings(
+            image_height=self.H, image_width=self.W, tanfovx=c["tanfovx"], tanfovy=c["tanfovy"], bg=self.bg,
+            scale_modifier=1.0, viewmatrix=cm[0:16].view(4, 4), projmatrix=cm[16:32].view(4, 4),
+            sh_degree=self.scene["sh_degree"], campos=cm[32:35], prefiltered=False, debug=False)
+
+    def view_fwd_bwd(self, v):
+        p = self.params
+        color, radii = self.dgr.GaussianRasterizer(self.settings(v))(
+            means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"], shs=p["shs"],
+            scales=p["scales"], rotations=p["rotations"])
+        self.last_fn, self.last_radii = color.grad_fn, radii
+        self.torch.autograd.backward([color], [self.dev_dL[v]])
+
+    def step(self, dist=None):
+        self.flat_grad.zero_()
+        for v in range(len(self.cams)):
+            self.view_fwd_bwd(v)
+        if dist is not None:
+            dist.all_reduce(self.flat_grad)
+
+    def step_e2e(self, dist=None):
+        t = self.torch
+        self.flat_param.copy_(self.host_param, non_blocking=True)
+        self.dev_cam.copy_(self.host_cam, non_blocking=True)
+        self.flat_grad.zero_()
+        for v in range(len(self.cams)):
+            self.dev_dL[v].copy_(self.host_dL[v], non_blocking=True)
+            self.view_fwd_bwd(v)
+        if dist is not None:
+            dist.all_reduce(self.flat_grad)
+        self.host_grad.copy_(self.flat_grad, non_blocking=True)
+        t.cuda.current_stream().synchronize()
+        return float(self.host_grad[0])
+
+
+def timed(torch, dist, fn, steps, warmup, dev):
+    """K steps between barrier + synchronize, CUDA events on the current stream, max over ranks (ms)."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = torch.tensor([a.elapsed_time(b)], device=dev)
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def fetch_u32(torch, wl, name):
+    """Internal array of the last forward (gsr_debug_fetch), as a uint32 numpy array."""
+    import ctypes as C
+    from diff_gaussian_rasterization import _abi
+    lib, fn = _abi.lib(), wl.last_fn
+    geom, image = fn.saved_tensors[9], fn.saved_tensors[11]
+    pv = lambda t: C.c_void_p(t.data_ptr())
+    n = lib.gsr_debug_fetch(name.encode(), wl.P, wl.W, wl.H, fn.num_rendered, pv(geom), pv(image), None, None, 0, None)
+    buf = torch.empty(int(n), dtype=torch.uint8, device=wl.dev)
+    lib.gsr_debug_fetch(name.encode(), wl.P, wl.W, wl.H, fn.num_rendered, pv(geom), pv(image), None, pv(buf), n, None)
+    torch.cuda.synchronize()
+    return buf.cpu().numpy().view(np.uint32)
+
+
+def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
+    """Per-stage average duration (CUDA events on the launching stream, gsr_profile_*) and roofline
+    fractions from the algorithmic bytes of SURVEY.md section 8(d) / DESIGN.md."""
+    import ctypes as C
+    from diff_gaussian_rasterization import _abi
+    lib = _abi.lib()
+    lib.gsr_profile_enable(1)
+    for _ in range(steps):
+        wl.step(None)
+    ms = (C.c_float * len(_abi.STAGES))()
+    calls = (C.c_int32 * len(_abi.STAGES))()
+    lib.gsr_profile_read(ms, calls)
+    lib.gsr_profile_enable(0)
+    P, L = wl.P, wl.last_fn.num_rendered
+    V = int((wl.last_radii > 0).sum().item())
+    n_contrib = fetch_u32(torch, wl, "n_contrib")
+    pairs = int(n_contrib.astype(np.int64).sum())
+    tiles = ((wl.W + 15) // 16) * ((wl.H + 15) // 16)
+    end_bit = 32 + max(1, int(tiles).bit_length())
+    passes = (end_bit + 7) // 8
+    HW = wl.W * wl.H
+    alg = {  # algorithmic bytes per launch (per view)
+        "preprocess_fwd": 311 * V + 20 * (P - V),
+        "duplicate_keys": 20 * P + 12 * L,
+        "sort": (8 + 24 * passes) * L,
+        "tile_ranges": 8 * L + 8 * tiles,
+        "blend_fwd": 40 * L + 20 * HW,
+        "blend_bwd": 40 * L + 20 * HW + 36 * L,
+        "preprocess_bwd": 559 * V + 300 * P,
+    }
+    # blend stages are FP32-issue bound: instructions per examined (pixel, Gaussian) pair
+    fp32_instr = {"blend_fwd": 20, "blend_bwd": 45}
+    fp32_peak = 148 * 128 * sm_max_mhz * 1e6  # lane-instructions / s
+    out, total = {}, 0.0
+    for i, name in enumerate(_abi.STAGES):
+        n = max(int(calls[i]), 1)
+        avg = float(ms[i]) / n
+        total += avg
+        e = {"ms": avg, "calls": int(calls[i]), "alg_bytes": int(alg[name]),
+             "hbm_gbs": alg[name] / (avg * 1e-3) / 1e9 if avg > 0 else None}
+        e["hbm_frac"] = e["hbm_gbs"] / hbm_peak if e["hbm_gbs"] else None
+        if name in fp32_instr:
+            e["bound"] = "fp32-issue"
+            e["pairs_lower_bound"] = pairs
+            e["fp32_frac"] = pairs * fp32_instr[name] / (avg * 1e-3) / fp32_peak if avg > 0 else None
+        else:
+            e["bound"] = "hbm"
+        out[name] = e
+    for e in out.values():
+        e["share"] = e["ms"] / total if total > 0 else None
+    return out, {"P": P, "V": V, "L": int(L), "sum_n_contrib": pairs, "tiles": tiles, "sort_passes": passes}
+
+
+def run_gsr(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    from diff_gaussian_rasterization import _abi
+    lib = _abi.lib()  # fails loudly if the CUDA library is missing
+    wl = Workload(args, torch, rank, world, dev)
+    hbm_peak, peak_src, sm_max = load_peaks()
+
+    # ---- value: inputs resident in HBM
+    sampler = ClockSampler(local) if rank == 0 else None
+    for _ in range(args.warmup):
+        wl.step(dist)
+    torch.cuda.synchronize()
+    lib.gsr_launch_count(1)
+    if sampler:
+        sampler.start()
+    ms = timed(torch, dist, lambda: wl.step(dist), args.steps, 0, dev)
+    clocks = sampler.stop() if sampler else None
+    launches = int(lib.gsr_launch_count(1))
+    views_total = world * len(wl.cams) * args.steps
+    value = views_total / (ms * 1e-3)
+
+    # ---- e2e: host buffers in, host gradients out, every step
+    e2e = None
+    if not args.no_e2e:
+        ms_e = timed(torch, dist, lambda: wl.step_e2e(dist), args.steps, max(1, args.warmup - 1), dev)
+        e2e = {"value": views_total / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(wl.h2d_bytes),
+               "d2h_bytes_per_step": int(wl.d2h_bytes), "ms_per_step": ms_e / args.steps}
+
+    # ---- per-stage timing (rank 0 reports; every rank runs it to stay in lock-step)
+    stages, counts = stage_table(torch, wl, max(1, min(args.steps, 5)), hbm_peak, sm_max)
+    if dist is not None:
+        dist.barrier()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    top = max(stages, key=lambda k: stages[k]["ms"])
+    t = stages[top]
+    if t["bound"] == "hbm":
+        roofline = {"kernel": top, "bound": "hbm", "achieved": t["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s",
+                    "frac": t["hbm_frac"], "traffic": None, "peak_source": peak_src}
+    else:
+        fp32_peak_t = 148 * 128 * sm_max * 1e6 / 1e12
+        roofline = {"kernel": top, "bound": "fp32-issue", "achieved": t["fp32_frac"] * fp32_peak_t, "peak": fp32_peak_t,
+                    "unit": "T lane-instr/s", "frac": t["fp32_frac"], "traffic": None,
+                    "hbm_view": {"achieved": t["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": t["hbm_frac"]},
+                    "peak_source": "148 SM x 128 FP32 lanes x sm_max_mhz; HBM " + peak_src}
+    c = wl.scene["cam"]
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {wl.P} Gaussians SH3, {c['image_width']}x{c['image_height']}, fwd+bwd",
+                   "views_per_rank_per_step": len(wl.cams), "parallelism": f"view-sharded x{world}, replicated Gaussians"
+                   + (", NCCL all-reduce of attribute gradients per step" if world > 1 else ""),
+                   "l2": "inputs larger than L2 (236 MB of attributes + 25 MB dL/dpixel per view)", **counts},
+        "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "stages": stages,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        steps_c = 1
+        vps, dt, cores, n = cpu_views_per_sec(wl.scene, wl.cams, steps_c, 0, args.cpu_sample_views)
+        line["cpu_baseline"] = {"value": vps, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{n} full view(s) fwd+bwd of the same workload, {dt:.1f} s, OpenMP over all host cores"}
+    if args.stages_out:
+        json.dump({"stages": stages, "counts": counts}, open(args.stages_out, "w"), indent=1)
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_gsr(a)

@@ -120,6 +120,16 @@ int gsr_sort_pairs_u64(const uint64_t* keys_in, uint64_t* keys_out, const uint32
 int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64_t L, const void* geom,
                         const void* image, const void* scratch, void* dst, int64_t cap, void* stream);
 
+/* ---- measurement hooks (bench.py): per-stage CUDA-event timing on the launching stream and a
+ *      count of kernel launches.  Stage order: preprocess_fwd, duplicate_keys, sort, tile_ranges,
+ *      blend_fwd, blend_bwd, preprocess_bwd (GSR_STAGE_COUNT entries).  gsr_profile_read
+ *      synchronises on the recorded events, sums milliseconds / calls per stage since the last
+ *      read and clears the records. ---- */
+#define GSR_STAGE_COUNT 7
+int gsr_profile_enable(int on);
+int gsr_profile_read(float* ms_host, int32_t* calls_host);
+int64_t gsr_launch_count(int reset);
+
 /* Host helper: number of key bits the tile id needs (getHigherMsb, rasterizer_impl.cu:35-50). */
 uint32_t gsr_higher_msb(uint32_t n);
 
