@@ -12,6 +12,26 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libdgr_ref.so")
 
 
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+# scene recipes of the committed fixtures (tools/make_golden.py ran the reference CUDA on them)
+GOLDEN_SCENES = {
+    "tiny_sh3": dict(name="tiny"),
+    "tiny_sh1_bg": dict(name="tiny", seed=77, sh_degree=1, width=150, height=100),
+    "tiny_precomp": dict(name="tiny", seed=78, width=200, height=136),
+}
+
+
+def golden_case(name):
+    """(scene, kwargs for run_gsr/run_oracle, dict of reference-CUDA outputs) of a committed fixture."""
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    scene = make_scene(**GOLDEN_SCENES[name])
+    kw = {k[3:]: z[k] for k in z.files if k.startswith("in_")}
+    gold = {k: z[k] for k in z.files if not k.startswith(("in_", "grad_"))}
+    gold["grads"] = {k[5:]: z[k] for k in z.files if k.startswith("grad_")}
+    gold["num_rendered"] = int(gold["num_rendered"])
+    return scene, kw, gold
+
+
 def settings_for(scene, device="cuda", debug=False, prefiltered=False, bg=None):
     from diff_gaussian_rasterization import GaussianRasterizationSettings
     c = scene["cam"]

@@ -1,0 +1,141 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads and exports every symbol that
+include/gsr_b200.h declares, host-only helpers agree with the oracle, and the Python package keeps
+the reference's API surface and error behaviour
+(DGR/diff_gaussian_rasterization/__init__.py:157-221).  No compute calls: there is no GPU here."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "gsr_b200.h")
+
+
+def _declared_symbols():
+    txt = open(HEADER).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(gsr_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_library_exports_every_declared_symbol():
+    from diff_gaussian_rasterization import _abi
+    lib = C.CDLL(_abi.LIB_PATH)
+    names = _declared_symbols()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in gsr_b200.h but not exported"
+    # and the ctypes table binds exactly the declared set
+    assert sorted(_abi.EXPORTS) == names
+
+
+def test_abi_version_and_struct_layout():
+    from diff_gaussian_rasterization import _abi
+    assert _abi.lib().gsr_abi_version() == _abi.ABI_VERSION
+    # 8 int32 + 4 float + 12 pointers
+    assert C.sizeof(_abi.GsrInputs) == 8 * 4 + 4 * 4 + 12 * 8
+
+
+def test_higher_msb_matches_reference_semantics():
+    """getHigherMsb (rasterizer_impl.cu:35-50): number of bits needed for the tile count."""
+    from diff_gaussian_rasterization import _abi
+    from oracle import cpu_ref
+    lib = _abi.lib()
+    for n, want in ((2500, 12), (8160, 13), (32400, 15), (1, 1), (2, 2), (255, 8), (256, 9), (65535, 16), (65536, 17)):
+        assert lib.gsr_higher_msb(n) == want
+        assert cpu_ref.higher_msb(n) == want
+    for n in range(1, 5000, 7):
+        assert lib.gsr_higher_msb(n) == cpu_ref.higher_msb(n) == n.bit_length()
+
+
+def test_buffer_size_queries_are_monotone_and_aligned():
+    from diff_gaussian_rasterization import _abi
+    lib = _abi.lib()
+    assert lib.gsr_geom_bytes(0) == 0
+    prev = 0
+    for P in (1, 1000, 100_000, 1_000_000):
+        b = lib.gsr_geom_bytes(P)
+        assert b % 256 == 0 and b > prev and b >= 79 * P
+        prev = b
+    assert lib.gsr_image_bytes(1920, 1080) >= 8 * 1920 * 1080 + 8 * 8160
+    s0 = lib.gsr_scratch_bytes(1000, 0, 64, 64)
+    s1 = lib.gsr_scratch_bytes(1000, 100_000, 64, 64)
+    assert s1 - s0 >= 20 * 100_000
+    assert lib.gsr_sort_temp_bytes(1 << 20) >= 12 * (1 << 20)
+
+
+def test_invalid_arguments_return_status_and_message():
+    from diff_gaussian_rasterization import _abi
+    lib = _abi.lib()
+    r = lib.gsr_forward_geometry(None, None, None, None, 0, None, None, None)
+    assert r == _abi.GSR_ERR_INVALID and b"NULL" in lib.gsr_last_error()
+    inp = _abi.GsrInputs()
+    inp.P, inp.W, inp.H = 10, 0, 16
+    assert lib.gsr_forward_geometry(C.byref(inp), None, None, None, 0, None, None, None) == _abi.GSR_ERR_INVALID
+    assert lib.gsr_sort_pairs_u64(None, None, None, None, -1, 32, None, 0, None) == _abi.GSR_ERR_INVALID
+    assert lib.gsr_sort_pairs_u64(None, None, None, None, 0, 32, None, 0, None) == _abi.GSR_OK  # empty sort
+    assert lib.gsr_mark_visible(0, None, None, None, None, None) == _abi.GSR_OK
+    with pytest.raises(Exception):
+        _abi.check(_abi.GSR_ERR_INVALID, "x")
+    with pytest.raises(RuntimeError):
+        _abi.check(_abi.GSR_ERR_CUDA, "x")
+
+
+# ---------------------------------------------------------------- Python API surface
+def test_public_names_and_settings_fields():
+    import diff_gaussian_rasterization as dgr
+    for n in ("GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians", "_RasterizeGaussians"):
+        assert hasattr(dgr, n)
+    assert dgr.GaussianRasterizationSettings._fields == (
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+        "sh_degree", "campos", "prefiltered", "debug")
+    assert issubclass(dgr.GaussianRasterizer, torch.nn.Module)
+    assert issubclass(dgr._RasterizeGaussians, torch.autograd.Function)
+
+
+def _settings():
+    import diff_gaussian_rasterization as dgr
+    e = torch.eye(4)
+    return dgr.GaussianRasterizationSettings(16, 16, 1.0, 1.0, torch.zeros(3), 1.0, e, e, 3, torch.zeros(3), False, False)
+
+
+def test_argument_exclusivity_errors_match_reference():
+    """__init__.py:191-195: plain Exception with the reference's messages."""
+    import diff_gaussian_rasterization as dgr
+    r = dgr.GaussianRasterizer(_settings())
+    m3, m2, op = torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 1)
+    sh, col = torch.zeros(4, 16, 3), torch.zeros(4, 3)
+    sc, rot, cov = torch.ones(4, 3), torch.zeros(4, 4), torch.zeros(4, 6)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(m3, m2, op, scales=sc, rotations=rot)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(m3, m2, op, shs=sh, colors_precomp=col, scales=sc, rotations=rot)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair or precomputed 3D covariance"):
+        r(m3, m2, op, shs=sh)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair or precomputed 3D covariance"):
+        r(m3, m2, op, shs=sh, scales=sc, rotations=rot, cov3D_precomp=cov)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair or precomputed 3D covariance"):
+        r(m3, m2, op, shs=sh, scales=sc)
+
+
+def test_cpu_tensors_fail_loudly_no_fallback():
+    import diff_gaussian_rasterization as dgr
+    r = dgr.GaussianRasterizer(_settings())
+    m3, m2, op = torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 1)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        r(m3, m2, op, shs=torch.zeros(4, 16, 3), scales=torch.ones(4, 3), rotations=torch.zeros(4, 4))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        r.markVisible(m3)
+    with pytest.raises(RuntimeError, match=r"\(num_points, 3\)"):
+        r(torch.zeros(4, 4), m2, op, shs=torch.zeros(4, 16, 3), scales=torch.ones(4, 3), rotations=torch.zeros(4, 4))
+
+
+def test_product_never_imports_oracle():
+    """The product package must not reach into oracle/ (it is the checker, not a fallback)."""
+    pkg = os.path.join(ROOT, "3d-gaussian-splat-attack_b200")
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                src = open(os.path.join(d, f), errors="replace").read()
+                assert "cpu_ref" not in src and "liboracle" not in src and "oracle/" not in src.replace("oracle/_ref", ""), f
