@@ -341,6 +341,49 @@ def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
     return out, {"P": P, "V": V, "L": int(L), "sum_n_contrib": pairs, "tiles": tiles, "sort_passes": passes}
 
 
+def ref_cuda_views_per_sec(torch, wl, n_views):
+    """The reference's own CUDA rasterizer (unmodified DGR/cuda_rasterizer sources compiled for sm_100a behind
+    oracle/ref_shim.cu -> oracle/_ref/libdgr_ref.so) on the same B200, same inputs, fwd+bwd per view, including the
+    zero-filled output / gradient tensors its torch glue allocates per call (rasterize_points.cu:68-78,151-159).
+    A second baseline (north_star); None when the library did not travel."""
+    import ctypes as C
+    so = os.path.join(ROOT, "oracle", "_ref", "libdgr_ref.so")
+    if not os.path.exists(so):
+        return None
+    L = C.CDLL(so)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    P, W, H, pr = wl.P, wl.W, wl.H, wl.params
+    det = {k: v.detach() for k, v in pr.items()}
+
+    def one(v):
+        c, cm = wl.cams[v], wl.dev_cam[v]
+        out = torch.zeros((3, H, W), device=wl.dev)
+        radii = torch.zeros((P,), dtype=torch.int32, device=wl.dev)
+        R = L.ref_forward(P, 3, 16, p(wl.bg), W, H, p(det["means3D"]), p(det["shs"]), None, p(det["opacities"]),
+                          p(det["scales"]), C.c_float(1.0), p(det["rotations"]), None, p(cm[0:16]), p(cm[16:32]),
+                          p(cm[32:35]), C.c_float(c["tanfovx"]), C.c_float(c["tanfovy"]), 0, p(out), p(radii), 0)
+        assert R >= 0
+        z = lambda *s: torch.zeros(s, device=wl.dev)
+        g = [z(P, 3), z(P, 4), z(P, 1), z(P, 3), z(P, 3), z(P, 6), z(P, 16, 3), z(P, 3), z(P, 4)]
+        r = L.ref_backward(P, 3, 16, R, p(wl.bg), W, H, p(det["means3D"]), p(det["shs"]), None, p(det["scales"]),
+                           C.c_float(1.0), p(det["rotations"]), None, p(cm[0:16]), p(cm[16:32]), p(cm[32:35]),
+                           C.c_float(c["tanfovx"]), C.c_float(c["tanfovy"]), p(radii), p(wl.dev_dL[v]),
+                           *[p(t) for t in g], 0)
+        assert r == 0
+
+    nv = len(wl.cams)
+    for v in range(min(2, nv)):
+        one(v)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(n_views):
+        one(i % nv)
+    b.record()
+    torch.cuda.synchronize()
+    return n_views / (a.elapsed_time(b) * 1e-3)
+
+
 def run_gsr(args):
     import torch
     rank = int(os.environ.get("RANK", "0"))
@@ -415,6 +458,11 @@ def run_gsr(args):
         vps, dt, cores, n = cpu_views_per_sec(wl.scene, wl.cams, steps_c, 0, args.cpu_sample_views)
         line["cpu_baseline"] = {"value": vps, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{n} full view(s) fwd+bwd of the same workload, {dt:.1f} s, OpenMP over all host cores"}
+    if world == 1:
+        rc = ref_cuda_views_per_sec(torch, wl, 2 * len(wl.cams))
+        line["ref_cuda_baseline"] = None if rc is None else {
+            "value": rc, "unit": UNIT, "what": "reference CUDA rasterizer (DGR sources, sm_100a build) on this B200, "
+            "same inputs, legacy default stream, incl. its per-call zero-filled tensors"}
     if args.stages_out:
         json.dump({"stages": stages, "counts": counts}, open(args.stages_out, "w"), indent=1)
     print(json.dumps(line), flush=True)

@@ -67,7 +67,7 @@ def run_gsr(scene, grad=True, fetch=True, obj=None, bg=None, colors_precomp=None
     """Forward (+backward) through the public Python API; returns dict of numpy arrays."""
     import diff_gaussian_rasterization as dgr
     rs = settings_for(scene, bg=bg)
-    t = scene_tensors(scene, requires_grad=grad)
+    t = scene_tensors(scene, requires_grad=grad or fetch)  # a grad_fn is needed to reach the saved state
     P = scene["P"]
     means2D = torch.zeros((P, 3), device="cuda", requires_grad=grad)
     kw = {}
