@@ -11,24 +11,35 @@
 // The contribution test uses exactly the forward arithmetic, so the set of contributing pairs is
 // the forward's.  Sum order differs from the reference's atomics -> gradients are compared with
 // a tolerance.  Bound: FP32 issue + shuffle + L2 reduction throughput.
-#include "common.cuh"
-#include "fp_exact.cuh"
+#include "blend_common.cuh"
 
 namespace gsr {
 namespace {
-
-constexpr int BATCH = TILE_PIX;
-
-__device__ __forceinline__ float gauss_power(float dx, float dy, float A, float B, float C) {
-  using namespace fpx;
-  const float q = fma_(dx, mul(dx, A), mul(dy, mul(dy, C)));
-  return sub(mul(q, -0.5f), mul(dy, mul(dx, B)));
-}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
+}
+
+// one exchange step of the multi-value butterfly: lanes with `upper` keep `hi` and send `lo`, the others
+// the opposite; both end up with the pair-sum of the value they kept
+__device__ __forceinline__ float xchg_add(float lo, float hi, int off, bool upper) {
+  const float send = upper ? lo : hi, mine = upper ? hi : lo;
+  return mine + __shfl_xor_sync(0xffffffffu, send, off);
+}
+
+// Sums 8 values across the warp with 9 shuffles (instead of 40): after the call the lane whose low two bits
+// are 0 holds the warp total of value index (lane >> 2).
+__device__ __forceinline__ float warp_sum8(const float* v, int lane) {
+  const bool u16 = lane & 16, u8 = lane & 8, u4 = lane & 4;
+  const float w0 = xchg_add(v[0], v[4], 16, u16), w1 = xchg_add(v[1], v[5], 16, u16);
+  const float w2 = xchg_add(v[2], v[6], 16, u16), w3 = xchg_add(v[3], v[7], 16, u16);
+  const float x0 = xchg_add(w0, w2, 8, u8), x1 = xchg_add(w1, w3, 8, u8);
+  float y = xchg_add(x0, x1, 4, u4);
+  y += __shfl_xor_sync(0xffffffffu, y, 2);
+  y += __shfl_xor_sync(0xffffffffu, y, 1);
+  return y;  // value index = 4*bit4 + 2*bit3 + bit2 of the lane
 }
 
 template <int K>
@@ -39,16 +50,15 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const float* __restrict__ obj_feats, const float* __restrict__ final_T,
                  const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
                  const float* __restrict__ dL_dobjpix, float* __restrict__ accum, float* __restrict__ dL_dobj) {
-  __shared__ float4 s_a[BATCH];  // x, y, conic.x, conic.y
-  __shared__ float4 s_b[BATCH];  // conic.z, opacity, threshold, r
-  __shared__ float2 s_c[BATCH];  // g, b
-  __shared__ uint32_t s_id[BATCH];
+  __shared__ BlendStage S;
+  __shared__ uint32_t s_id[BLEND_BATCH];
   __shared__ uint32_t s_max;
 
-  const int tid = threadIdx.y * TILE_X + threadIdx.x, lane = tid & 31;
-  const uint32_t px = blockIdx.x * TILE_X + threadIdx.x, py = blockIdx.y * TILE_Y + threadIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t wx0 = blockIdx.x * TILE_X + (warp & 1) * WARP_W, wy0 = blockIdx.y * TILE_Y + (warp >> 1) * WARP_H;
+  const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-  const float pxf = (float)px, pyf = (float)py;
+  const float pxf = (float)px, pyf = (float)py, wx0f = (float)wx0, wy0f = (float)wy0;
   const size_t HW = (size_t)W * H, pid = (size_t)py * W + px;
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
 
@@ -74,94 +84,92 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   __syncthreads();
   const uint32_t n_live = min(s_max, range.y - range.x);  // entries [0, n_live) can matter to this tile
 
-  // batches walk the list back to front: batch b covers list positions n_live-1-b*BATCH-j
-  for (uint32_t done_cnt = 0; done_cnt < n_live; done_cnt += BATCH) {
+  // batches walk the list back to front: slot j of a batch holds list position n_live-1-done_cnt-j
+  for (uint32_t done_cnt = 0; done_cnt < n_live; done_cnt += BLEND_BATCH) {
     __syncthreads();
     if (done_cnt + tid < n_live) {
-      const uint32_t pos = n_live - 1 - done_cnt - tid;
-      const uint32_t g = point_list[range.x + pos];
-      const float2 xy = means2D[g];
-      const float4 co = conic_opacity[g];
-      const float4 ct = rgb_thr[g];
-      s_a[tid] = make_float4(xy.x, xy.y, co.x, co.y);
-      s_b[tid] = make_float4(co.z, co.w, ct.w, ct.x);
-      s_c[tid] = make_float2(ct.y, ct.z);
+      const uint32_t g = point_list[range.x + (n_live - 1 - done_cnt - tid)];
+      stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr);
       s_id[tid] = g;
     }
     __syncthreads();
-    const int nb = (int)min((uint32_t)BATCH, n_live - done_cnt);
-    for (int j = 0; j < nb; j++) {
-      const uint32_t pos = n_live - 1 - done_cnt - j;  // 0-based position in the tile list
-      if (pos >= warp_last) continue;                   // warp-uniform
-      const float4 a = s_a[j];
-      const float4 b = s_b[j];
-      const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
-      const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-      bool hit = pos < my_last && !(power > 0.0f || power < b.z);
-      float G = 0.f, alpha = 0.f;
-      if (hit) {
-        G = expf(power);
-        alpha = fminf(0.99f, fpx::mul(b.y, G));
-        hit = !(alpha < 1.0f / 255.0f);
-      }
-      if (!__any_sync(0xffffffffu, hit)) continue;
-      float v[9 + (K > 0 ? K : 0)];
-#pragma unroll
-      for (int k = 0; k < 9 + (K > 0 ? K : 0); k++) v[k] = 0.f;
-      if (hit) {
-        const float2 c = s_c[j];
-        const float col[3] = {b.w, c.x, c.y};
-        const float inv = __frcp_rn(1.f - alpha);
-        T = T * inv;
-        const float w = alpha * T;
-        float dL_dalpha = 0.f;
-#pragma unroll
-        for (int ch = 0; ch < 3; ch++) {
-          acc_r[ch] = last_alpha * last_c[ch] + (1.f - last_alpha) * acc_r[ch];
-          last_c[ch] = col[ch];
-          dL_dalpha += (col[ch] - acc_r[ch]) * dpix[ch];
-          v[ch] = w * dpix[ch];
+    const int nb = (int)min((uint32_t)BLEND_BATCH, n_live - done_cnt);
+    const uint32_t top = n_live - 1 - done_cnt;  // list position of slot 0
+    for (int r = 0; r < nb; r += 32) {
+      const int jl = r + lane;
+      bool keep = false;
+      if (jl < nb && top - jl < warp_last) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
+      uint32_t mask = __ballot_sync(0xffffffffu, keep);
+      while (mask) {
+        const int j = r + __ffs(mask) - 1;
+        mask &= mask - 1;
+        const uint32_t pos = top - j;
+        const float4 a = S.a[j];
+        const float4 b = S.b[j];
+        const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
+        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
+        bool hit = pos < my_last && !(power > 0.0f || power < b.z);
+        float G = 0.f, alpha = 0.f;
+        if (hit) {
+          G = expf(power);
+          alpha = fminf(0.99f, fpx::mul(b.y, G));
+          hit = !(alpha < 1.0f / 255.0f);
         }
-        if (K > 0) {
-          const float* f = obj_feats + (size_t)s_id[j] * K;
+        if (!__any_sync(0xffffffffu, hit)) continue;
+        float v[9 + (K > 0 ? K : 0)];
 #pragma unroll
-          for (int k = 0; k < K; k++) {
-            const float o = __ldg(f + k);
-            acc_o[k] = last_alpha * last_o[k] + (1.f - last_alpha) * acc_o[k];
-            last_o[k] = o;
-            dL_dalpha += (o - acc_o[k]) * dpo[k];
-            v[9 + k] = w * dpo[k];
+        for (int k = 0; k < 9 + (K > 0 ? K : 0); k++) v[k] = 0.f;
+        if (hit) {
+          const float4 c = S.c[j];
+          const float col[3] = {b.w, c.x, c.y};
+          const float inv = __frcp_rn(1.f - alpha);
+          T = T * inv;
+          const float w = alpha * T;
+          float dL_dalpha = 0.f;
+#pragma unroll
+          for (int ch = 0; ch < 3; ch++) {
+            acc_r[ch] = last_alpha * last_c[ch] + (1.f - last_alpha) * acc_r[ch];
+            last_c[ch] = col[ch];
+            dL_dalpha += (col[ch] - acc_r[ch]) * dpix[ch];
+            v[ch] = w * dpix[ch];
+          }
+          if (K > 0) {
+            const float* f = obj_feats + (size_t)s_id[j] * K;
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+              const float o = __ldg(f + k);
+              acc_o[k] = last_alpha * last_o[k] + (1.f - last_alpha) * acc_o[k];
+              last_o[k] = o;
+              dL_dalpha += (o - acc_o[k]) * dpo[k];
+              v[9 + k] = w * dpo[k];
+            }
+          }
+          dL_dalpha *= T;
+          last_alpha = alpha;
+          dL_dalpha += (-T_final * inv) * bg_dot;
+          const float dL_dG = b.y * dL_dalpha;
+          const float gdx = G * dx, gdy = G * dy;
+          const float dG_ddelx = -gdx * a.z - gdy * a.w;
+          const float dG_ddely = -gdy * b.x - gdx * a.w;
+          v[3] = dL_dG * dG_ddelx * ddelx_dx;
+          v[4] = dL_dG * dG_ddely * ddely_dy;
+          v[5] = -0.5f * gdx * dx * dL_dG;
+          v[6] = -0.5f * gdx * dy * dL_dG;
+          v[7] = -0.5f * gdy * dy * dL_dG;
+          v[8] = G * dL_dalpha;
+        }
+        const float s8 = warp_sum8(v, lane);
+        const float s1 = warp_sum(v[8]);
+        const uint32_t g = s_id[j];
+        if ((lane & 3) == 0) atomicAdd(accum + (size_t)g * 12 + (lane >> 2), s8);
+        if (lane == 1) atomicAdd(accum + (size_t)g * 12 + 8, s1);
+        if (K > 0) {
+          const float o8a = warp_sum8(v + 9, lane), o8b = warp_sum8(v + 9 + (K > 8 ? 8 : 0), lane);
+          if ((lane & 3) == 0) {
+            atomicAdd(dL_dobj + (size_t)g * K + (lane >> 2), o8a);
+            if (K > 8) atomicAdd(dL_dobj + (size_t)g * K + 8 + (lane >> 2), o8b);
           }
         }
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final * inv) * bg_dot;
-        const float dL_dG = b.y * dL_dalpha;
-        const float gdx = G * dx, gdy = G * dy;
-        const float dG_ddelx = -gdx * a.z - gdy * a.w;
-        const float dG_ddely = -gdy * b.x - gdx * a.w;
-        v[3] = dL_dG * dG_ddelx * ddelx_dx;
-        v[4] = dL_dG * dG_ddely * ddely_dy;
-        v[5] = -0.5f * gdx * dx * dL_dG;
-        v[6] = -0.5f * gdx * dy * dL_dG;
-        v[7] = -0.5f * gdy * dy * dL_dG;
-        v[8] = G * dL_dalpha;
-      }
-#pragma unroll
-      for (int k = 0; k < 9 + (K > 0 ? K : 0); k++) v[k] = warp_sum(v[k]);
-      const uint32_t g = s_id[j];
-      if (lane < 9) {
-        // lane k adds value k (select without dynamic register indexing)
-        float out = v[0];
-#pragma unroll
-        for (int k = 1; k < 9; k++) out = lane == k ? v[k] : out;
-        atomicAdd(accum + (size_t)g * 12 + lane, out);
-      }
-      if (K > 0 && lane >= 16) {
-        float out = v[9];
-#pragma unroll
-        for (int k = 1; k < K; k++) out = (lane - 16) == k ? v[9 + k] : out;
-        atomicAdd(dL_dobj + (size_t)g * K + (lane - 16), out);
       }
     }
   }
@@ -171,7 +179,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 
 int launch_blend_bwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
                      const float* dL_dpix, const float* dL_dobjpix, float* accum, float* dL_dobj, cudaStream_t st) {
-  const dim3 grid((in.W + TILE_X - 1) / TILE_X, (in.H + TILE_Y - 1) / TILE_Y), block(TILE_X, TILE_Y);
+  const dim3 grid((in.W + TILE_X - 1) / TILE_X, (in.H + TILE_Y - 1) / TILE_Y), block(TILE_PIX);
   GSR_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)in.P * 12 * sizeof(float), st));
   if (in.K > 0) GSR_CUDA_CHECK(cudaMemsetAsync(dL_dobj, 0, (size_t)in.P * in.K * sizeof(float), st));
 #define GSR_BLEND_BWD(KK)                                                                                      \

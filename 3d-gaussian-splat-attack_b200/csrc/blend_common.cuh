@@ -1,0 +1,64 @@
+// blend_common.cuh -- pieces shared by the forward and backward blending kernels.
+#pragma once
+#include "common.cuh"
+#include "fp_exact.cuh"
+
+namespace gsr {
+
+constexpr int BLEND_BATCH = TILE_PIX;  // list entries staged per block iteration
+// A 256-thread block owns one 16x16 tile; each warp owns an 8x4 pixel rectangle of it
+// (warp w: columns (w&1)*8.., rows (w>>1)*4..; lane l: column l&7, row l>>3).
+constexpr int WARP_W = 8, WARP_H = 4;
+
+// power = -0.5 (A dx^2 + C dy^2) - B dx dy with the roundings of the reference build
+// (forward.cu:335, backward.cu:490); see fp_exact.cuh.
+__device__ __forceinline__ float gauss_power(float dx, float dy, float A, float B, float C) {
+  using namespace fpx;
+  const float q = fma_(dx, mul(dx, A), mul(dy, mul(dy, C)));
+  return sub(mul(q, -0.5f), mul(dy, mul(dx, B)));
+}
+
+// One staged list entry (shared memory, SoA of vector words).
+struct BlendStage {
+  float4 a[BLEND_BATCH];  // x, y, conic A, conic B
+  float4 b[BLEND_BATCH];  // conic C, opacity, power threshold, r
+  float4 c[BLEND_BATCH];  // g, b, -B/C, -B/A
+};
+
+__device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g, const float2* __restrict__ means2D,
+                                            const float4* __restrict__ conic_opacity,
+                                            const float4* __restrict__ rgb_thr) {
+  const float2 xy = means2D[g];
+  const float4 co = conic_opacity[g];
+  const float4 ct = rgb_thr[g];
+  S.a[slot] = make_float4(xy.x, xy.y, co.x, co.y);
+  S.b[slot] = make_float4(co.z, co.w, ct.w, ct.x);
+  S.c[slot] = make_float4(ct.y, ct.z, __fdividef(-co.y, co.z), __fdividef(-co.y, co.x));
+}
+
+// Conservative test of one list entry against a warp's pixel rectangle [x0, x0+WARP_W-1] x [y0, y0+WARP_H-1]:
+// returns false only if NO pixel of the rectangle can pass the per-pixel test `power >= threshold`.
+// f(u,v) = -0.5 (A u^2 + C v^2) - B u v is concave (the conic is positive definite), so its maximum over the
+// rectangle is 0 when the centre is inside and otherwise lies on an edge visible from the centre; the two
+// candidates below are the exact edge maxima (clamped 1-D maximisers).  The margin covers the rounding of
+// both this evaluation and the per-pixel one (each <= ~5e-7 * S, S = sum of the magnitudes of the terms,
+// bounded over the rectangle by Smax), so a pair that passes per pixel is never culled here.  NaNs compare
+// false and are kept.
+__device__ __forceinline__ bool rect_may_contribute(const float4 a, const float4 b, const float4 c, float x0,
+                                                    float y0) {
+  const float A = a.z, B = a.w, C = b.x, thr = b.z;
+  const float ux0 = x0 - a.x, ux1 = ux0 + (float)(WARP_W - 1);
+  const float vy0 = y0 - a.y, vy1 = vy0 + (float)(WARP_H - 1);
+  const float u1 = fminf(fmaxf(0.f, ux0), ux1);
+  const float v1 = fminf(fmaxf(c.z * u1, vy0), vy1);
+  const float v2 = fminf(fmaxf(0.f, vy0), vy1);
+  const float u2 = fminf(fmaxf(c.w * v2, ux0), ux1);
+  const float f1 = -0.5f * (A * u1 * u1 + C * v1 * v1) - B * u1 * v1;
+  const float f2 = -0.5f * (A * u2 * u2 + C * v2 * v2) - B * u2 * v2;
+  const float um = fmaxf(fabsf(ux0), fabsf(ux1)), vm = fmaxf(fabsf(vy0), fabsf(vy1));
+  const float smax = 0.5f * (A * um * um + C * vm * vm) + fabsf(B) * um * vm;
+  const bool degenerate = !(B * B < 0.99999f * (A * C));  // not safely positive definite: do not cull
+  return degenerate || !(fmaxf(f1, f2) + 2e-6f * smax + 1e-4f < thr);
+}
+
+}  // namespace gsr

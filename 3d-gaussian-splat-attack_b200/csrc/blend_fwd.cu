@@ -6,25 +6,18 @@
 //   * the per-Gaussian record (xy, conic, opacity, RGB) is staged once per batch as three vector
 //     words, so the inner loop reads only shared memory (the reference re-reads RGB from global
 //     memory for every contributing pixel, forward.cu:355);
+//   * each warp owns an 8x4 pixel rectangle and first tests 32 staged entries at a time, one per
+//     lane, against that rectangle (rect_may_contribute, conservative); only entries that can reach
+//     alpha >= 1/255 somewhere in the rectangle are then evaluated per pixel, in list order;
 //   * a per-Gaussian power threshold (computed in preprocess) rejects pairs whose alpha cannot
 //     reach 1/255 before the exponential is evaluated; pairs that pass go through exactly the
 //     reference's sequence (same expf, same roundings), so T, n_contrib and the colour are
 //     bit-identical.
 // Bound: FP32 issue + MUFU.EX2 (nothing here is bandwidth- or tensor-shaped).
-#include "common.cuh"
-#include "fp_exact.cuh"
+#include "blend_common.cuh"
 
 namespace gsr {
 namespace {
-
-constexpr int BATCH = TILE_PIX;
-
-// power = -0.5 (A dx^2 + C dy^2) - B dx dy, rounded step by step as the reference build does (see fp_exact.cuh)
-__device__ __forceinline__ float gauss_power(float dx, float dy, float A, float B, float C) {
-  using namespace fpx;
-  const float q = fma_(dx, mul(dx, A), mul(dy, mul(dy, C)));
-  return sub(mul(q, -0.5f), mul(dy, mul(dx, B)));
-}
 
 template <int K>
 __global__ void __launch_bounds__(TILE_PIX)
@@ -33,15 +26,14 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const float4* __restrict__ rgb_thr, const float* __restrict__ obj_feats,
                  const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                  float* __restrict__ out_color, float* __restrict__ out_objects) {
-  __shared__ float4 s_a[BATCH];  // x, y, conic.x, conic.y
-  __shared__ float4 s_b[BATCH];  // conic.z, opacity, threshold, r
-  __shared__ float2 s_c[BATCH];  // g, b
-  __shared__ uint32_t s_id[K > 0 ? BATCH : 1];
+  __shared__ BlendStage S;
+  __shared__ uint32_t s_id[K > 0 ? BLEND_BATCH : 1];
 
-  const int tid = threadIdx.y * TILE_X + threadIdx.x;
-  const uint32_t px = blockIdx.x * TILE_X + threadIdx.x, py = blockIdx.y * TILE_Y + threadIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t wx0 = blockIdx.x * TILE_X + (warp & 1) * WARP_W, wy0 = blockIdx.y * TILE_Y + (warp >> 1) * WARP_H;
+  const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-  const float pxf = (float)px, pyf = (float)py;
+  const float pxf = (float)px, pyf = (float)py, wx0f = (float)wx0, wy0f = (float)wy0;
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   int todo = (int)(range.y - range.x);
 
@@ -52,42 +44,47 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   for (int k = 0; k < (K > 0 ? K : 1); k++) O[k] = 0.f;
   uint32_t last_contributor = 0;
 
-  for (uint32_t base = range.x; base < range.y; base += BATCH, todo -= BATCH) {
+  for (uint32_t base = range.x; base < range.y; base += BLEND_BATCH, todo -= BLEND_BATCH) {
     if (__syncthreads_count(done) == TILE_PIX) break;
     if (base + tid < range.y) {
       const uint32_t g = point_list[base + tid];
-      const float2 xy = means2D[g];
-      const float4 co = conic_opacity[g];
-      const float4 ct = rgb_thr[g];
-      s_a[tid] = make_float4(xy.x, xy.y, co.x, co.y);
-      s_b[tid] = make_float4(co.z, co.w, ct.w, ct.x);
-      s_c[tid] = make_float2(ct.y, ct.z);
+      stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr);
       if (K > 0) s_id[tid] = g;
     }
     __syncthreads();
-    const int nb = min(BATCH, todo);
+    const int nb = min(BLEND_BATCH, todo);
     const uint32_t first = base - range.x;
-    for (int j = 0; !done && j < nb; j++) {
-      const float4 a = s_a[j];
-      const float4 b = s_b[j];
-      const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
-      const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-      if (power > 0.0f || power < b.z) continue;
-      const float alpha = fminf(0.99f, fpx::mul(b.y, expf(power)));
-      if (alpha < 1.0f / 255.0f) continue;
-      const float test_T = fpx::mul(T, fpx::sub(1.0f, alpha));
-      if (test_T < 0.0001f) { done = true; continue; }
-      const float2 c = s_c[j];
-      C0 = fpx::fma_(T, fpx::mul(alpha, b.w), C0);
-      C1 = fpx::fma_(T, fpx::mul(alpha, c.x), C1);
-      C2 = fpx::fma_(T, fpx::mul(alpha, c.y), C2);
-      if (K > 0) {
-        const float* f = obj_feats + (size_t)s_id[j] * K;
+    for (int r = 0; r < nb; r += 32) {
+      if (__all_sync(0xffffffffu, done)) break;
+      const int jl = r + lane;
+      bool keep = false;
+      if (jl < nb) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
+      uint32_t mask = __ballot_sync(0xffffffffu, keep);
+      while (mask) {
+        const int j = r + __ffs(mask) - 1;
+        mask &= mask - 1;
+        if (done) continue;
+        const float4 a = S.a[j];
+        const float4 b = S.b[j];
+        const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
+        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
+        if (power > 0.0f || power < b.z) continue;
+        const float alpha = fminf(0.99f, fpx::mul(b.y, expf(power)));
+        if (alpha < 1.0f / 255.0f) continue;
+        const float test_T = fpx::mul(T, fpx::sub(1.0f, alpha));
+        if (test_T < 0.0001f) { done = true; continue; }
+        const float4 c = S.c[j];
+        C0 = fpx::fma_(T, fpx::mul(alpha, b.w), C0);
+        C1 = fpx::fma_(T, fpx::mul(alpha, c.x), C1);
+        C2 = fpx::fma_(T, fpx::mul(alpha, c.y), C2);
+        if (K > 0) {
+          const float* f = obj_feats + (size_t)s_id[j] * K;
 #pragma unroll
-        for (int k = 0; k < K; k++) O[k] = fpx::fma_(T, fpx::mul(alpha, __ldg(f + k)), O[k]);
+          for (int k = 0; k < K; k++) O[k] = fpx::fma_(T, fpx::mul(alpha, __ldg(f + k)), O[k]);
+        }
+        T = test_T;
+        last_contributor = first + j + 1;
       }
-      T = test_T;
-      last_contributor = first + j + 1;
     }
   }
   if (inside) {
@@ -108,7 +105,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 
 int launch_blend_fwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
                      float* out_color, float* out_objects, cudaStream_t st) {
-  const dim3 grid((in.W + TILE_X - 1) / TILE_X, (in.H + TILE_Y - 1) / TILE_Y), block(TILE_X, TILE_Y);
+  const dim3 grid((in.W + TILE_X - 1) / TILE_X, (in.H + TILE_Y - 1) / TILE_Y), block(TILE_PIX);
 #define GSR_BLEND_FWD(KK)                                                                                     \
   blend_fwd_kernel<KK><<<grid, block, 0, st>>>(im.ranges, point_list, in.W, in.H, g.means2D, g.conic_opacity, \
                                                g.rgb_thr, in.obj_feats, in.bg, im.final_T, im.n_contrib,      \
