@@ -95,6 +95,12 @@ int gsr_profile_read(float* ms_host, int32_t* calls_host) {
   return GSR_OK;
 }
 
+int gsr_debug_counters(uint64_t* out_host, int reset) {
+  if (!out_host) { set_error("debug_counters: NULL"); return GSR_ERR_INVALID; }
+  GSR_TRY(blend_fwd_stats(out_host, reset));
+  return blend_bwd_stats(out_host + 8, reset);
+}
+
 size_t gsr_geom_bytes(int32_t P) { return Geom(nullptr, P).bytes; }
 size_t gsr_image_bytes(int32_t W, int32_t H) { return Image(nullptr, W, H).bytes; }
 size_t gsr_scratch_bytes(int32_t P, int64_t L_cap, int32_t, int32_t) { return Scratch(nullptr, P, L_cap).bytes; }

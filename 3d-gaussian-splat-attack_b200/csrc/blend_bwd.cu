@@ -100,6 +100,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       bool keep = false;
       if (jl < nb && top - jl < warp_last) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
       uint32_t mask = __ballot_sync(0xffffffffu, keep);
+      GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
       while (mask) {
         const int j = r + __ffs(mask) - 1;
         mask &= mask - 1;
@@ -116,6 +117,9 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           hit = !(alpha < 1.0f / 255.0f);
         }
         if (!__any_sync(0xffffffffu, hit)) continue;
+#ifdef GSR_STATS
+        { const uint32_t hm = __ballot_sync(0xffffffffu, hit); GSR_STAT(3, 1); GSR_STAT(4, __popc(hm)); }
+#endif
         float v[9 + (K > 0 ? K : 0)];
 #pragma unroll
         for (int k = 0; k < 9 + (K > 0 ? K : 0); k++) v[k] = 0.f;
@@ -176,6 +180,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 }
 
 }  // namespace
+
+int blend_bwd_stats(uint64_t* out_host, int reset) { return read_blend_stats(out_host, reset); }
 
 int launch_blend_bwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
                      const float* dL_dpix, const float* dL_dobjpix, float* accum, float* dL_dobj, cudaStream_t st) {

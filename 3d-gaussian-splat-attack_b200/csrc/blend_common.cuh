@@ -10,6 +10,24 @@ constexpr int BLEND_BATCH = TILE_PIX;  // list entries staged per block iteratio
 // (warp w: columns (w&1)*8.., rows (w>>1)*4..; lane l: column l&7, row l>>3).
 constexpr int WARP_W = 8, WARP_H = 4;
 
+// Optional instrumentation (make STATS=1): [0] cull rounds, [1] entries tested, [2] entries kept,
+// [3] (warp, entry) evaluations with >= 1 contributing lane, [4] contributing (pixel, entry) pairs,
+// [5] lanes active at evaluation.  One copy per translation unit (forward / backward).
+static __device__ unsigned long long g_blend_stats[8];
+inline int read_blend_stats(uint64_t* out_host, int reset) {
+  if (cudaMemcpyFromSymbol(out_host, g_blend_stats, 8 * sizeof(uint64_t)) != cudaSuccess) return GSR_ERR_CUDA;
+  if (reset) {
+    const unsigned long long z[8] = {0};
+    if (cudaMemcpyToSymbol(g_blend_stats, z, sizeof(z)) != cudaSuccess) return GSR_ERR_CUDA;
+  }
+  return GSR_OK;
+}
+#ifdef GSR_STATS
+#define GSR_STAT(i, n) do { if ((threadIdx.x & 31) == 0) atomicAdd(&g_blend_stats[i], (unsigned long long)(n)); } while (0)
+#else
+#define GSR_STAT(i, n) do { } while (0)
+#endif
+
 // power = -0.5 (A dx^2 + C dy^2) - B dx dy with the roundings of the reference build
 // (forward.cu:335, backward.cu:490); see fp_exact.cuh.
 __device__ __forceinline__ float gauss_power(float dx, float dy, float A, float B, float C) {

@@ -60,9 +60,13 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       bool keep = false;
       if (jl < nb) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
       uint32_t mask = __ballot_sync(0xffffffffu, keep);
+      GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
       while (mask) {
         const int j = r + __ffs(mask) - 1;
         mask &= mask - 1;
+#ifdef GSR_STATS
+        { const uint32_t act = __ballot_sync(__activemask(), !done); GSR_STAT(5, __popc(act)); }
+#endif
         if (done) continue;
         const float4 a = S.a[j];
         const float4 b = S.b[j];
@@ -84,6 +88,9 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         }
         T = test_T;
         last_contributor = first + j + 1;
+#ifdef GSR_STATS
+        atomicAdd(&g_blend_stats[4], 1ull);
+#endif
       }
     }
   }
@@ -102,6 +109,8 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 }
 
 }  // namespace
+
+int blend_fwd_stats(uint64_t* out_host, int reset) { return read_blend_stats(out_host, reset); }
 
 int launch_blend_fwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
                      float* out_color, float* out_objects, cudaStream_t st) {

@@ -165,6 +165,8 @@ int launch_preprocess_bwd(const gsr_inputs& in, const Geom& g, const int32_t* ra
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 
 uint32_t higher_msb(uint32_t n);
+int blend_fwd_stats(uint64_t* out_host, int reset);
+int blend_bwd_stats(uint64_t* out_host, int reset);
 
 // ---- per-stage profiling (gsr_profile_*): CUDA events on the launching stream around each stage,
 // and a count of kernel launches (gsr_launch_count) ------------------------------------------------

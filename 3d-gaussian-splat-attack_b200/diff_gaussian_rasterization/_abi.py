@@ -49,6 +49,7 @@ EXPORTS = {
     "gsr_profile_enable": (C.c_int, [C.c_int]),
     "gsr_profile_read": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gsr_launch_count": (C.c_int64, [C.c_int]),
+    "gsr_debug_counters": (C.c_int, [C.c_void_p, C.c_int]),
     "gsr_debug_fetch": (C.c_int64, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
 }

@@ -1,0 +1,97 @@
+"""View-sharded data parallelism for multi-view attack steps (new; no counterpart in the reference,
+which loops over the cameras of a batch serially on one GPU, attack.py:481-484).
+
+The path shards by camera view: every rank holds the full Gaussian set,
+renders the views k with k % world == rank, accumulates attribute gradients locally and the ranks
+sum them with ONE all-reduce per PGD step.  The gradient tensors of all attributes are views into
+one flat fp32 buffer, which is the collective's bucket (no pack / unpack copies).  Works with any
+torch.distributed backend: NCCL over NVLink on the GPU box, gloo in the CPU tests.
+"""
+from typing import Callable, Dict, Iterable, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+__all__ = ["shard_views", "FlatGradBucket", "sharded_step"]
+
+
+def shard_views(n_views: int, rank: int, world: int) -> List[int]:
+    """Indices of the views rank `rank` renders: k = rank, rank + world, ... (round-robin keeps ring-neighbour
+    cameras, whose cost is similar, on different ranks)."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError(f"bad rank/world {rank}/{world}")
+    return list(range(rank, n_views, world))
+
+
+class FlatGradBucket:
+    """One flat fp32 gradient buffer shared by all attribute tensors.
+
+    `params` maps names to leaf tensors (xyz, SH, scale, rotation, opacity ...).  After construction each
+    p.grad is a view into `self.flat`, so autograd accumulates per-view gradients straight into the bucket
+    and `all_reduce()` is a single collective over it.
+    """
+
+    def __init__(self, params: Dict[str, torch.Tensor]):
+        if not params:
+            raise ValueError("no parameters")
+        ps = list(params.values())
+        dev, dt = ps[0].device, ps[0].dtype
+        for n, p in params.items():
+            if not p.is_leaf or not p.requires_grad:
+                raise ValueError(f"{n}: must be a leaf tensor that requires grad")
+            if p.device != dev or p.dtype != dt:
+                raise ValueError(f"{n}: all parameters must share device and dtype")
+        self.params = dict(params)
+        self.numel = sum(p.numel() for p in ps)
+        self.flat = torch.zeros(self.numel, dtype=dt, device=dev)
+        self.slices = {}
+        off = 0
+        for n, p in self.params.items():
+            self.slices[n] = (off, off + p.numel())
+            p.grad = self.flat[off:off + p.numel()].view(p.shape)
+            off += p.numel()
+
+    def zero(self):
+        self.flat.zero_()
+        for n, p in self.params.items():  # re-bind in case an optimizer step replaced .grad (set_to_none=True)
+            a, b = self.slices[n]
+            if p.grad is None or p.grad.data_ptr() != self.flat.data_ptr() + a * self.flat.element_size():
+                p.grad = self.flat[a:b].view(p.shape)
+
+    def grad(self, name: str) -> torch.Tensor:
+        a, b = self.slices[name]
+        return self.flat[a:b].view(self.params[name].shape)
+
+    def all_reduce(self, group=None, async_op: bool = False):
+        """SUM over ranks, in place.  No-op without an initialised process group or with world size 1."""
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return None
+        return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+    def global_norm(self) -> torch.Tensor:
+        """L2 norm of the (already reduced) gradient: what the L2 PGD variants need (attack.py:25-173)."""
+        return self.flat.norm()
+
+
+def sharded_step(views: Sequence, render_backward: Callable[[object], Optional[torch.Tensor]], bucket: FlatGradBucket,
+                 rank: Optional[int] = None, world: Optional[int] = None, group=None) -> torch.Tensor:
+    """One gradient step over `views` (any per-view objects, e.g. cameras), sharded over the ranks.
+
+    `render_backward(view)` must render the view, evaluate its loss and call backward (gradients land in the
+    bucket); it may return the scalar loss.  Returns the loss summed over ALL views (all-reduced), after the
+    bucket holds the gradient summed over all views -- identical on every rank, so applying the same PGD update
+    keeps the replicas in sync without a broadcast.
+    """
+    on = dist.is_available() and dist.is_initialized()
+    rank = (dist.get_rank(group) if on else 0) if rank is None else rank
+    world = (dist.get_world_size(group) if on else 1) if world is None else world
+    bucket.zero()
+    total = torch.zeros((), dtype=bucket.flat.dtype, device=bucket.flat.device)
+    for k in shard_views(len(views), rank, world):
+        loss = render_backward(views[k])
+        if loss is not None:
+            total = total + loss.detach().to(total.dtype)
+    bucket.all_reduce(group)
+    if on and world > 1:
+        dist.all_reduce(total, op=dist.ReduceOp.SUM, group=group)
+    return total

@@ -129,6 +129,9 @@ int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64
 int gsr_profile_enable(int on);
 int gsr_profile_read(float* ms_host, int32_t* calls_host);
 int64_t gsr_launch_count(int reset);
+/* 16 counters of the blend kernels (8 forward, 8 backward), non-zero only in a `make STATS=1` build:
+ * cull rounds, entries tested, entries kept, warp evaluations with a hit, contributing pairs, active lanes. */
+int gsr_debug_counters(uint64_t* out_host, int reset);
 
 /* Host helper: number of key bits the tile id needs (getHigherMsb, rasterizer_impl.cu:35-50). */
 uint32_t gsr_higher_msb(uint32_t n);

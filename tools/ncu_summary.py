@@ -1,0 +1,32 @@
+"""Summarises an .ncu-rep (read here, no GPU): python tools/ncu_summary.py gpurun_out/prof.ncu-rep [kernel-substring]"""
+import csv
+import io
+import subprocess
+import sys
+
+rep = sys.argv[1]
+filt = sys.argv[2] if len(sys.argv) > 2 else ""
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+H = rows[0]
+KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread",
+        "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
+        "smsp__thread_inst_executed_per_inst_executed.ratio",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__t_sector_hit_rate.pct", "lts__t_sectors_op_red.sum",
+        "lts__t_sectors_op_atom.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_active"]
+stall = [h for h in H if "warp_issue_stalled" in h and h.endswith("_per_warp_active.pct")]
+ki = H.index("Kernel Name")
+for r in rows[2:]:
+    if filt and filt not in r[ki]:
+        continue
+    print("====", r[ki][:90])
+    for k in KEYS:
+        if k in H:
+            print(f"  {k:72s} {r[H.index(k)]}")
+    st = sorted(((float(r[H.index(s)].replace(',', '') or 0), s) for s in stall), reverse=True)[:7]
+    for v, s in st:
+        print(f"  stall {s.replace('smsp__warp_issue_stalled_', '').replace('_per_warp_active.pct', ''):40s} {v:.1f}")
