@@ -7,6 +7,10 @@
 //   * the 9 per-Gaussian partials (3 colour, 2 mean2D, 3 conic, 1 opacity) are reduced across the
 //     warp with shuffles before one RED per value per warp (the reference issues 9 atomics per
 //     contributing pixel, backward.cu:523-554), and only when some lane contributes;
+//   * what is accumulated per Gaussian is linear in the per-pixel weight w = G dL/dalpha: 3 colour sums,
+//     sum w, and the first / second moments of w about the centre (w dx, w dy, w dx^2, w dx dy, w dy^2);
+//     preprocess_bwd turns the moments into dL/dmean2D, dL/dconic and dL/dopacity (same algebra as
+//     backward.cu:523-554, factored so the per-pixel work is 6 multiplies);
 //   * partials land in one packed [P][12] accumulator, so a Gaussian's 9 words share two sectors.
 // The contribution test uses exactly the forward arithmetic, so the set of contributing pairs is
 // the forward's.  Sum order differs from the reference's atomics -> gradients are compared with
@@ -42,6 +46,12 @@ __device__ __forceinline__ float warp_sum8(const float* v, int lane) {
   return y;  // value index = 4*bit4 + 2*bit3 + bit2 of the lane
 }
 
+__device__ __forceinline__ float fast_rcp(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 template <int K>
 __global__ void __launch_bounds__(TILE_PIX)
 blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
@@ -53,8 +63,10 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   __shared__ BlendStage S;
   __shared__ uint32_t s_id[BLEND_BATCH];
   __shared__ uint32_t s_max;
+  __shared__ uint8_t s_q[TILE_PIX / 32][32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t wx0 = blockIdx.x * TILE_X + (warp & 1) * WARP_W, wy0 = blockIdx.y * TILE_Y + (warp >> 1) * WARP_H;
   const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
@@ -99,11 +111,13 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       const int jl = r + lane;
       bool keep = false;
       if (jl < nb && top - jl < warp_last) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
-      uint32_t mask = __ballot_sync(0xffffffffu, keep);
+      const uint32_t mask = __ballot_sync(0xffffffffu, keep);
       GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
-      while (mask) {
-        const int j = r + __ffs(mask) - 1;
-        mask &= mask - 1;
+      if (keep) s_q[warp][__popc(mask & lt_mask)] = (uint8_t)jl;
+      __syncwarp();
+      const int nk = __popc(mask);
+      for (int i = 0; i < nk; i++) {
+        const int j = s_q[warp][i];
         const uint32_t pos = top - j;
         const float4 a = S.a[j];
         const float4 b = S.b[j];
@@ -120,13 +134,14 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 #ifdef GSR_STATS
         { const uint32_t hm = __ballot_sync(0xffffffffu, hit); GSR_STAT(3, 1); GSR_STAT(4, __popc(hm)); }
 #endif
+        // v[0..2] colour, v[3..7] first/second moments of w = G dL/dalpha about the Gaussian centre, v[8] = sum w
         float v[9 + (K > 0 ? K : 0)];
 #pragma unroll
         for (int k = 0; k < 9 + (K > 0 ? K : 0); k++) v[k] = 0.f;
         if (hit) {
           const float4 c = S.c[j];
           const float col[3] = {b.w, c.x, c.y};
-          const float inv = __frcp_rn(1.f - alpha);
+          const float inv = fast_rcp(1.f - alpha);
           T = T * inv;
           const float w = alpha * T;
           float dL_dalpha = 0.f;
@@ -151,16 +166,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           dL_dalpha *= T;
           last_alpha = alpha;
           dL_dalpha += (-T_final * inv) * bg_dot;
-          const float dL_dG = b.y * dL_dalpha;
-          const float gdx = G * dx, gdy = G * dy;
-          const float dG_ddelx = -gdx * a.z - gdy * a.w;
-          const float dG_ddely = -gdy * b.x - gdx * a.w;
-          v[3] = dL_dG * dG_ddelx * ddelx_dx;
-          v[4] = dL_dG * dG_ddely * ddely_dy;
-          v[5] = -0.5f * gdx * dx * dL_dG;
-          v[6] = -0.5f * gdx * dy * dL_dG;
-          v[7] = -0.5f * gdy * dy * dL_dG;
-          v[8] = G * dL_dalpha;
+          const float m0 = G * dL_dalpha, m1 = m0 * dx, m2 = m0 * dy;
+          v[3] = m1; v[4] = m2; v[5] = m1 * dx; v[6] = m1 * dy; v[7] = m2 * dy; v[8] = m0;
         }
         const float s8 = warp_sum8(v, lane);
         const float s1 = warp_sum(v[8]);

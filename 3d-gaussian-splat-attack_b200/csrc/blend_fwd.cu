@@ -28,8 +28,10 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  float* __restrict__ out_color, float* __restrict__ out_objects) {
   __shared__ BlendStage S;
   __shared__ uint32_t s_id[K > 0 ? BLEND_BATCH : 1];
+  __shared__ uint8_t s_q[TILE_PIX / 32][32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t wx0 = blockIdx.x * TILE_X + (warp & 1) * WARP_W, wy0 = blockIdx.y * TILE_Y + (warp >> 1) * WARP_H;
   const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
@@ -59,20 +61,22 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       const int jl = r + lane;
       bool keep = false;
       if (jl < nb) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
-      uint32_t mask = __ballot_sync(0xffffffffu, keep);
+      const uint32_t mask = __ballot_sync(0xffffffffu, keep);
       GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
-      while (mask) {
-        const int j = r + __ffs(mask) - 1;
-        mask &= mask - 1;
+      // compact the kept slots into this warp's queue (list order is preserved)
+      if (keep) s_q[warp][__popc(mask & lt_mask)] = (uint8_t)jl;
+      __syncwarp();
+      const int nk = __popc(mask);
+      for (int i = 0; i < nk; i++) {
+        const int j = s_q[warp][i];
 #ifdef GSR_STATS
         { const uint32_t act = __ballot_sync(__activemask(), !done); GSR_STAT(5, __popc(act)); }
 #endif
-        if (done) continue;
         const float4 a = S.a[j];
         const float4 b = S.b[j];
         const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
         const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-        if (power > 0.0f || power < b.z) continue;
+        if (done || power > 0.0f || power < b.z) continue;
         const float alpha = fminf(0.99f, fpx::mul(b.y, expf(power)));
         if (alpha < 1.0f / 255.0f) continue;
         const float test_T = fpx::mul(T, fpx::sub(1.0f, alpha));

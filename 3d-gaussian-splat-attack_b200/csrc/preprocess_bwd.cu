@@ -79,7 +79,15 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
     const float4* ap = reinterpret_cast<const float4*>(accum) + (size_t)idx * 3;
     a0 = ap[0]; a1 = ap[1]; a8 = ap[2].x;
   }
-  // a0 = dcolor.rgb, dmean2D.x ; a1 = dmean2D.y, dconic.x, dconic.y, dconic.w ; a8 = dopacity
+  // accumulated by blend_bwd: a0 = dcolor.rgb, sum w dx ; a1 = sum w dy, sum w dx^2, sum w dx dy, sum w dy^2 ;
+  // a8 = sum w  (w = G dL/dalpha).  Convert to dL/dmean2D, dL/dconic, dL/dopacity (backward.cu:523-554):
+  if (live) {
+    const float4 co = g.conic_opacity[idx];
+    const float m1 = a0.w, m2 = a1.x, op = co.w;
+    a0.w = op * (0.5f * in.W) * (-co.x * m1 - co.y * m2);
+    a1.x = op * (0.5f * in.H) * (-co.z * m2 - co.y * m1);
+    a1.y *= -0.5f * op; a1.z *= -0.5f * op; a1.w *= -0.5f * op;
+  }
   dL_dmean2D[3 * (size_t)idx] = a0.w; dL_dmean2D[3 * (size_t)idx + 1] = a1.x; dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
   dL_dopacity[idx] = a8;
   if (dL_dcolor) { dL_dcolor[3 * (size_t)idx] = a0.x; dL_dcolor[3 * (size_t)idx + 1] = a0.y; dL_dcolor[3 * (size_t)idx + 2] = a0.z; }

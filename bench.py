@@ -184,14 +184,14 @@ class Workload:
         self.host_param = torch.from_numpy(host).pin_memory()
         self.host_grad = torch.empty_like(self.host_param).pin_memory()
         self.flat_param = self.host_param.to(dev)
-        self.flat_grad = torch.zeros_like(self.flat_param)
+        from diff_gaussian_rasterization.dist import FlatGradBucket
         self.params, off = {}, 0
         for n, k in ATTRS:
             sz = self.P * k
-            p = self.flat_param[off:off + sz].view(SHAPES[n]).detach().requires_grad_(True)
-            p.grad = self.flat_grad[off:off + sz].view(SHAPES[n])
-            self.params[n] = p
+            self.params[n] = self.flat_param[off:off + sz].view(SHAPES[n]).detach().requires_grad_(True)
             off += sz
+        self.bucket = FlatGradBucket(self.params)  # every .grad is a view into bucket.flat (the NCCL bucket)
+        self.flat_grad = self.bucket.flat
         self.means2D = torch.zeros((self.P, 3), device=dev)  # dummy screen-space tensor (no grad wanted)
         rng = np.random.default_rng(99 + rank)
         nv = len(self.cams)
