@@ -3,38 +3,54 @@
 // Replaces renderCUDA<3> backward (DGR/cuda_rasterizer/backward.cu:399-557).  Same per-pixel
 // recurrence (recompute alpha, rebuild T by division, running accum_rec), but:
 //   * the walk starts at the tile's largest n_contrib instead of the end of the tile list, and a
-//     warp skips entries beyond its own largest n_contrib;
-//   * the 9 per-Gaussian partials (3 colour, 2 mean2D, 3 conic, 1 opacity) are reduced across the
-//     warp with shuffles before one RED per value per warp (the reference issues 9 atomics per
-//     contributing pixel, backward.cu:523-554), and only when some lane contributes;
-//   * what is accumulated per Gaussian is linear in the per-pixel weight w = G dL/dalpha: 3 colour sums,
-//     sum w, and the first / second moments of w about the centre (w dx, w dy, w dx^2, w dx dy, w dy^2);
-//     preprocess_bwd turns the moments into dL/dmean2D, dL/dconic and dL/dopacity (same algebra as
-//     backward.cu:523-554, factored so the per-pixel work is 6 multiplies);
-//   * partials land in one packed [P][12] accumulator, so a Gaussian's 9 words share two sectors.
+//     warp (an 8x4 pixel rectangle) skips entries beyond its own largest n_contrib and entries
+//     that cannot reach alpha >= 1/255 inside its rectangle (rect_may_contribute);
+//   * what is accumulated per Gaussian is linear in two per-pixel weights, wc = alpha*T and
+//     w = G dL/dalpha: 3 colour sums (wc dL/dpixel), sum w, and the first / second moments of w about
+//     the centre (w dx, w dy, w dx^2, w dx dy, w dy^2); preprocess_bwd turns the moments into
+//     dL/dmean2D, dL/dconic and dL/dopacity (same algebra as backward.cu:523-554);
+//   * the sum over the pixels of a Gaussian is done WITHOUT a per-entry cross-lane reduction:
+//     phase 1 (lane = pixel) runs the sequential per-pixel recurrence and writes (wc, w) of every
+//     (pixel, entry) pair of a group of 16 kept entries to a per-warp shared-memory panel;
+//     phase 2 (lane = entry x pixel-half) sweeps the panel, each lane accumulating the 9 sums of its
+//     own entry in registers, then one shuffle per value joins the two halves and one RED per value
+//     goes to the packed [P][12] accumulator (the reference issues 9 atomics per contributing pixel).
 // The contribution test uses exactly the forward arithmetic, so the set of contributing pairs is
 // the forward's.  Sum order differs from the reference's atomics -> gradients are compared with
-// a tolerance.  Bound: FP32 issue + shuffle + L2 reduction throughput.
+// a tolerance.  Bound: FP32 issue.
 #include "blend_common.cuh"
 
 namespace gsr {
 namespace {
+
+constexpr int GRP = 16;          // kept entries per phase-2 sweep
+constexpr int PANEL_STRIDE = 33; // float2 row stride of the panel (bank-conflict-free in both phases)
+constexpr int NWARP = TILE_PIX / 32;
+
+struct BwdWarp {
+  float2 panel[GRP][PANEL_STRIDE];  // [group slot][pixel lane] = (alpha*T, G*dL/dalpha); 0 when the pair does not contribute
+  float4 pix[32];                   // dL/dpixel (r, g, b, -) of each pixel lane
+  uint8_t q[32];                    // kept batch slots of the current cull round
+  uint8_t gj[GRP];                  // batch slot of each group entry
+};
+struct BwdSmem {
+  BlendStage S;
+  uint32_t id[BLEND_BATCH];
+  BwdWarp w[NWARP];
+  uint32_t smax;
+};
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
-
-// one exchange step of the multi-value butterfly: lanes with `upper` keep `hi` and send `lo`, the others
-// the opposite; both end up with the pair-sum of the value they kept
 __device__ __forceinline__ float xchg_add(float lo, float hi, int off, bool upper) {
   const float send = upper ? lo : hi, mine = upper ? hi : lo;
   return mine + __shfl_xor_sync(0xffffffffu, send, off);
 }
-
-// Sums 8 values across the warp with 9 shuffles (instead of 40): after the call the lane whose low two bits
-// are 0 holds the warp total of value index (lane >> 2).
+// Sums 8 values across the warp with 9 shuffles: the lane whose low two bits are 0 ends up holding the
+// warp total of value index (lane >> 2).  Used for the object-feature channels only.
 __device__ __forceinline__ float warp_sum8(const float* v, int lane) {
   const bool u16 = lane & 16, u8 = lane & 8, u4 = lane & 4;
   const float w0 = xchg_add(v[0], v[4], 16, u16), w1 = xchg_add(v[1], v[5], 16, u16);
@@ -43,13 +59,53 @@ __device__ __forceinline__ float warp_sum8(const float* v, int lane) {
   float y = xchg_add(x0, x1, 4, u4);
   y += __shfl_xor_sync(0xffffffffu, y, 2);
   y += __shfl_xor_sync(0xffffffffu, y, 1);
-  return y;  // value index = 4*bit4 + 2*bit3 + bit2 of the lane
+  return y;
 }
-
 __device__ __forceinline__ float fast_rcp(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
+}
+
+// Phase 2: lane (e = lane & 15, h = lane >> 4) sums, over pixel lanes h*16 .. h*16+15, the 9 per-Gaussian
+// quantities of group entry e; the two halves are joined with one shuffle per value and lanes < ng issue the REDs.
+__device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int lane, float wx0f, float wy0f,
+                                            float* __restrict__ accum) {
+  __syncwarp();
+  const int e = lane & (GRP - 1), h = lane >> 4;
+  float cx = 0.f, cy = 0.f;
+  uint32_t g = 0;
+  if (e < ng) {
+    const int j = Wp.gj[e];
+    cx = M.S.a[j].x; cy = M.S.a[j].y; g = M.id[j];
+  }
+  const float wyh = wy0f + (float)(2 * h);
+  const float2* row = &Wp.panel[e][h * 16];
+  const float4* pix = &Wp.pix[h * 16];
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, m0 = 0.f, m1 = 0.f, m2 = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    const float2 pr = row[i];
+    const float4 dp = pix[i];
+    const float dx = cx - (wx0f + (float)(i & 7)), dy = cy - (wyh + (float)(i >> 3));
+    s0 = fmaf(pr.x, dp.x, s0); s1 = fmaf(pr.x, dp.y, s1); s2 = fmaf(pr.x, dp.z, s2);
+    const float wx = pr.y * dx, wy = pr.y * dy;
+    m0 += pr.y; m1 += wx; m2 += wy;
+    mxx = fmaf(wx, dx, mxx); mxy = fmaf(wx, dy, mxy); myy = fmaf(wy, dy, myy);
+  }
+  s0 += __shfl_xor_sync(0xffffffffu, s0, 16); s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+  s2 += __shfl_xor_sync(0xffffffffu, s2, 16); m0 += __shfl_xor_sync(0xffffffffu, m0, 16);
+  m1 += __shfl_xor_sync(0xffffffffu, m1, 16); m2 += __shfl_xor_sync(0xffffffffu, m2, 16);
+  mxx += __shfl_xor_sync(0xffffffffu, mxx, 16); mxy += __shfl_xor_sync(0xffffffffu, mxy, 16);
+  myy += __shfl_xor_sync(0xffffffffu, myy, 16);
+  if (lane < ng) {
+    float* dst = accum + (size_t)g * 12;
+    atomicAdd(dst + 0, s0); atomicAdd(dst + 1, s1); atomicAdd(dst + 2, s2);
+    atomicAdd(dst + 3, m1); atomicAdd(dst + 4, m2);
+    atomicAdd(dst + 5, mxx); atomicAdd(dst + 6, mxy); atomicAdd(dst + 7, myy);
+    atomicAdd(dst + 8, m0);
+  }
+  __syncwarp();
 }
 
 template <int K>
@@ -60,12 +116,12 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const float* __restrict__ obj_feats, const float* __restrict__ final_T,
                  const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
                  const float* __restrict__ dL_dobjpix, float* __restrict__ accum, float* __restrict__ dL_dobj) {
-  __shared__ BlendStage S;
-  __shared__ uint32_t s_id[BLEND_BATCH];
-  __shared__ uint32_t s_max;
-  __shared__ uint8_t s_q[TILE_PIX / 32][32];
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BwdSmem& M = *reinterpret_cast<BwdSmem*>(smem_raw);
+  BlendStage& S = M.S;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  BwdWarp& Wp = M.w[warp];
   const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t wx0 = blockIdx.x * TILE_X + (warp & 1) * WARP_W, wy0 = blockIdx.y * TILE_Y + (warp >> 1) * WARP_H;
   const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
@@ -79,6 +135,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   float T = T_final;
   float dpix[3] = {0.f, 0.f, 0.f};
   if (inside) { dpix[0] = dL_dpix[pid]; dpix[1] = dL_dpix[HW + pid]; dpix[2] = dL_dpix[2 * HW + pid]; }
+  Wp.pix[lane] = make_float4(dpix[0], dpix[1], dpix[2], 0.f);
   float dpo[K > 0 ? K : 1], acc_o[K > 0 ? K : 1], last_o[K > 0 ? K : 1];
 #pragma unroll
   for (int k = 0; k < (K > 0 ? K : 1); k++) {
@@ -87,22 +144,22 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   }
   const float bg_dot = bg[0] * dpix[0] + bg[1] * dpix[1] + bg[2] * dpix[2];
   float acc_r[3] = {0.f, 0.f, 0.f}, last_c[3] = {0.f, 0.f, 0.f}, last_alpha = 0.f;
-  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
   const uint32_t warp_last = __reduce_max_sync(0xffffffffu, my_last);
-  if (tid == 0) s_max = 0;
+  if (tid == 0) M.smax = 0;
   __syncthreads();
-  if (lane == 0) atomicMax(&s_max, warp_last);
+  if (lane == 0) atomicMax(&M.smax, warp_last);
   __syncthreads();
-  const uint32_t n_live = min(s_max, range.y - range.x);  // entries [0, n_live) can matter to this tile
+  const uint32_t n_live = min(M.smax, range.y - range.x);  // entries [0, n_live) can matter to this tile
 
+  int ng = 0;  // entries in this warp's current group (warp-uniform)
   // batches walk the list back to front: slot j of a batch holds list position n_live-1-done_cnt-j
   for (uint32_t done_cnt = 0; done_cnt < n_live; done_cnt += BLEND_BATCH) {
     __syncthreads();
     if (done_cnt + tid < n_live) {
       const uint32_t g = point_list[range.x + (n_live - 1 - done_cnt - tid)];
       stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr);
-      s_id[tid] = g;
+      M.id[tid] = g;
     }
     __syncthreads();
     const int nb = (int)min((uint32_t)BLEND_BATCH, n_live - done_cnt);
@@ -113,11 +170,11 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       if (jl < nb && top - jl < warp_last) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
       const uint32_t mask = __ballot_sync(0xffffffffu, keep);
       GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
-      if (keep) s_q[warp][__popc(mask & lt_mask)] = (uint8_t)jl;
+      if (keep) Wp.q[__popc(mask & lt_mask)] = (uint8_t)jl;
       __syncwarp();
       const int nk = __popc(mask);
       for (int i = 0; i < nk; i++) {
-        const int j = s_q[warp][i];
+        const int j = Wp.q[i];
         const uint32_t pos = top - j;
         const float4 a = S.a[j];
         const float4 b = S.b[j];
@@ -134,55 +191,55 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 #ifdef GSR_STATS
         { const uint32_t hm = __ballot_sync(0xffffffffu, hit); GSR_STAT(3, 1); GSR_STAT(4, __popc(hm)); }
 #endif
-        // v[0..2] colour, v[3..7] first/second moments of w = G dL/dalpha about the Gaussian centre, v[8] = sum w
-        float v[9 + (K > 0 ? K : 0)];
+        float wc = 0.f, wg = 0.f;  // alpha*T and G*dL/dalpha of this pair
+        float vo[K > 0 ? K : 1];
 #pragma unroll
-        for (int k = 0; k < 9 + (K > 0 ? K : 0); k++) v[k] = 0.f;
+        for (int k = 0; k < (K > 0 ? K : 1); k++) vo[k] = 0.f;
         if (hit) {
           const float4 c = S.c[j];
           const float col[3] = {b.w, c.x, c.y};
           const float inv = fast_rcp(1.f - alpha);
           T = T * inv;
-          const float w = alpha * T;
+          wc = alpha * T;
+          const float keep_prev = 1.f - last_alpha;
           float dL_dalpha = 0.f;
 #pragma unroll
           for (int ch = 0; ch < 3; ch++) {
-            acc_r[ch] = last_alpha * last_c[ch] + (1.f - last_alpha) * acc_r[ch];
+            acc_r[ch] = last_alpha * last_c[ch] + keep_prev * acc_r[ch];
             last_c[ch] = col[ch];
             dL_dalpha += (col[ch] - acc_r[ch]) * dpix[ch];
-            v[ch] = w * dpix[ch];
           }
           if (K > 0) {
-            const float* f = obj_feats + (size_t)s_id[j] * K;
+            const float* f = obj_feats + (size_t)M.id[j] * K;
 #pragma unroll
             for (int k = 0; k < K; k++) {
               const float o = __ldg(f + k);
-              acc_o[k] = last_alpha * last_o[k] + (1.f - last_alpha) * acc_o[k];
+              acc_o[k] = last_alpha * last_o[k] + keep_prev * acc_o[k];
               last_o[k] = o;
               dL_dalpha += (o - acc_o[k]) * dpo[k];
-              v[9 + k] = w * dpo[k];
+              vo[k] = wc * dpo[k];
             }
           }
           dL_dalpha *= T;
           last_alpha = alpha;
           dL_dalpha += (-T_final * inv) * bg_dot;
-          const float m0 = G * dL_dalpha, m1 = m0 * dx, m2 = m0 * dy;
-          v[3] = m1; v[4] = m2; v[5] = m1 * dx; v[6] = m1 * dy; v[7] = m2 * dy; v[8] = m0;
+          wg = G * dL_dalpha;
         }
-        const float s8 = warp_sum8(v, lane);
-        const float s1 = warp_sum(v[8]);
-        const uint32_t g = s_id[j];
-        if ((lane & 3) == 0) atomicAdd(accum + (size_t)g * 12 + (lane >> 2), s8);
-        if (lane == 1) atomicAdd(accum + (size_t)g * 12 + 8, s1);
+        Wp.panel[ng][lane] = make_float2(wc, wg);
+        if (lane == 0) Wp.gj[ng] = (uint8_t)j;
         if (K > 0) {
-          const float o8a = warp_sum8(v + 9, lane), o8b = warp_sum8(v + 9 + (K > 8 ? 8 : 0), lane);
+          const uint32_t g = M.id[j];
+          const float o8a = warp_sum8(vo, lane), o8b = warp_sum8(vo + (K > 8 ? 8 : 0), lane);
           if ((lane & 3) == 0) {
             atomicAdd(dL_dobj + (size_t)g * K + (lane >> 2), o8a);
             if (K > 8) atomicAdd(dL_dobj + (size_t)g * K + 8 + (lane >> 2), o8b);
           }
         }
+        if (++ng == GRP) { flush_group(M, Wp, ng, lane, wx0f, wy0f, accum); ng = 0; }
       }
     }
+    // the staged batch is about to be replaced: finish the partial group that refers to it
+    if (ng > 0) { flush_group(M, Wp, ng, lane, wx0f, wy0f, accum); ng = 0; }
   }
 }
 
@@ -195,10 +252,15 @@ int launch_blend_bwd(const gsr_inputs& in, const Geom& g, const Image& im, const
   const dim3 grid((in.W + TILE_X - 1) / TILE_X, (in.H + TILE_Y - 1) / TILE_Y), block(TILE_PIX);
   GSR_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)in.P * 12 * sizeof(float), st));
   if (in.K > 0) GSR_CUDA_CHECK(cudaMemsetAsync(dL_dobj, 0, (size_t)in.P * in.K * sizeof(float), st));
-#define GSR_BLEND_BWD(KK)                                                                                      \
-  blend_bwd_kernel<KK><<<grid, block, 0, st>>>(im.ranges, point_list, in.W, in.H, in.bg, g.means2D,            \
-                                               g.conic_opacity, g.rgb_thr, in.obj_feats, im.final_T,          \
-                                               im.n_contrib, dL_dpix, dL_dobjpix, accum, dL_dobj)
+#define GSR_BLEND_BWD(KK)                                                                                       \
+  do {                                                                                                          \
+    GSR_CUDA_CHECK(cudaFuncSetAttribute(blend_bwd_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                        (int)sizeof(BwdSmem)));                                                 \
+    blend_bwd_kernel<KK><<<grid, block, sizeof(BwdSmem), st>>>(im.ranges, point_list, in.W, in.H, in.bg,        \
+                                                               g.means2D, g.conic_opacity, g.rgb_thr,           \
+                                                               in.obj_feats, im.final_T, im.n_contrib, dL_dpix, \
+                                                               dL_dobjpix, accum, dL_dobj);                     \
+  } while (0)
   if (in.K == 0) GSR_BLEND_BWD(0);
   else if (in.K == 16) GSR_BLEND_BWD(16);
   else { set_error("object channels K=%d unsupported (0 or 16)", in.K); return GSR_ERR_INVALID; }
