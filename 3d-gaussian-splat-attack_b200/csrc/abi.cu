@@ -121,6 +121,12 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   Scratch s(scratch, in->P, 0);
   { StageScope ps(ST_PREPROCESS_FWD, st); GSR_TRY(launch_preprocess_fwd(*in, g, radii, s, num_rendered_dev, st)); }
   GSR_TRY(debug_sync(in, st, "preprocess"));
+  // order the Gaussians by (depth bits, index): 4 passes, the result lands back in (dkeys_a, geom.perm)
+  { StageScope ps(ST_SORT, st);
+    GSR_TRY(launch_sort_pairs_pingpong_u32(s.dkeys_a, g.perm, s.dkeys_b, s.dvals_b, in->P, 32, s.sort_temp, nullptr, st)); }
+  GSR_TRY(debug_sync(in, st, "depth_sort"));
+  { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, st)); }
+  GSR_TRY(debug_sync(in, st, "sorted_scan"));
   if (num_rendered_host)
     GSR_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, 4, cudaMemcpyDeviceToHost, st));
   if (in->prefiltered) {
@@ -153,21 +159,20 @@ int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* ra
   Image im(image, in->W, in->H);
   Scratch s(scratch, in->P, L);
   const int gx = (in->W + TILE_X - 1) / TILE_X, gy = (in->H + TILE_Y - 1) / TILE_Y;
-  const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));
+  const int end_bit = (int)higher_msb((uint32_t)(gx * gy));
   const int passes = (end_bit + 7) / 8;
-  // pass p reads pair (p&1) and writes the other: start in the pair that makes the result land in
-  // (keys_b, point_list)
-  uint64_t* k0 = (passes & 1) ? s.keys_a : s.keys_b;
-  uint64_t* k1 = (passes & 1) ? s.keys_b : s.keys_a;
+  // pass p reads pair (p&1) and writes the other: start in the pair that makes the result land in point_list
+  uint32_t* k0 = (passes & 1) ? s.tkeys_b : s.tkeys_a;
+  uint32_t* k1 = (passes & 1) ? s.tkeys_a : s.tkeys_b;
   uint32_t* v0 = (passes & 1) ? s.vals_a : point_list;
   uint32_t* v1 = (passes & 1) ? point_list : s.vals_a;
   if (L > 0) {
-    { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_duplicate_keys(in->P, g, radii, gx, k0, v0, st)); }
-    GSR_TRY(debug_sync(in, st, "duplicate_keys"));
-    { StageScope ps(ST_SORT, st); GSR_TRY(launch_sort_pairs_pingpong(k0, v0, k1, v1, L, end_bit, s.sort_temp, nullptr, st)); }
+    { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_duplicate_tiles(in->P, g, gx, k0, v0, st)); }
+    GSR_TRY(debug_sync(in, st, "duplicate_tiles"));
+    { StageScope ps(ST_SORT, st); GSR_TRY(launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, L, end_bit, s.sort_temp, nullptr, st)); }
     GSR_TRY(debug_sync(in, st, "sort"));
   }
-  { StageScope ps(ST_RANGES, st); GSR_TRY(launch_tile_ranges(L, s.keys_b, im.ranges, gx * gy, st)); }
+  { StageScope ps(ST_RANGES, st); GSR_TRY(launch_tile_ranges(L, s.tkeys_a, im.ranges, gx * gy, st)); }
   GSR_TRY(debug_sync(in, st, "tile_ranges"));
   { StageScope ps(ST_BLEND_FWD, st); GSR_TRY(launch_blend_fwd(*in, g, im, point_list, out_color, out_objects, st)); }
   GSR_TRY(debug_sync(in, st, "blend_fwd"));
@@ -230,12 +235,12 @@ int gsr_sort_pairs_u64(const uint64_t* keys_in, uint64_t* keys_out, const uint32
 }
 
 int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64_t L, const void* geom,
-                        const void* image, const void* scratch, void* dst, int64_t cap, void* stream) {
+                        const void* image, const void* scratch, const uint32_t* point_list, void* dst, int64_t cap,
+                        void* stream) {
   Geom g(const_cast<void*>(geom), P);
   Image im(const_cast<void*>(image), W, H);
   Scratch s(const_cast<void*>(scratch), P, L);
   const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
-  const int passes = (32 + (int)higher_msb((uint32_t)(gx * gy)) + 7) / 8;
   const size_t n = (size_t)P, HW = (size_t)W * H;
   const void* src = nullptr;
   size_t bytes = 0;
@@ -243,13 +248,21 @@ int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64
   F("depths", g.depths, n * 4) F("means2D", g.means2D, n * 8) F("cov3D", g.cov3D, n * 24)
   F("conic_opacity", g.conic_opacity, n * 16) F("rgb", g.rgb_thr, n * 16) F("clamped", g.clamped, n)
   F("tiles_touched", g.tiles_touched, n * 4) F("point_offsets", g.point_offsets, n * 4) F("rects", g.rects, n * 8)
+  F("perm", g.perm, n * 4) F("offsets_sorted", g.offsets_sorted, n * 4)
   F("final_T", im.final_T, HW * 4) F("n_contrib", im.n_contrib, HW * 4) F("ranges", im.ranges, (size_t)gx * gy * 8)
-  F("keys_sorted", s.keys_b, (size_t)L * 8)
-  // the unsorted pairs survive only when the pass count is odd (they are the ping-pong partner otherwise)
-  if (passes & 1) { F("keys_unsorted", s.keys_a, (size_t)L * 8) F("vals_unsorted", s.vals_a, (size_t)L * 4) }
+  F("tiles_sorted", s.tkeys_a, (size_t)L * 4)
 #undef F
-  if (!src) { set_error("debug_fetch: unknown or unavailable array '%s'", name); return GSR_ERR_INVALID; }
-  if (dst) {
+  if (!strcmp(name, "keys_sorted")) {
+    // the reference's sorted 64-bit keys (tile << 32 | depth bits), rebuilt from the sorted tile ids + point list
+    bytes = (size_t)L * 8;
+    if (dst) {
+      if (!scratch || !point_list || cap < (int64_t)bytes) { set_error("debug_fetch: keys_sorted needs scratch, point_list and cap >= 8 L"); return GSR_ERR_INVALID; }
+      GSR_TRY(launch_rebuild_keys(L, s.tkeys_a, point_list, g.depths, (uint64_t*)dst, (cudaStream_t)stream));
+    }
+    return (int64_t)bytes;
+  }
+  if (!src && bytes == 0 && strcmp(name, "tiles_sorted")) { set_error("debug_fetch: unknown array '%s'", name); return GSR_ERR_INVALID; }
+  if (dst && bytes) {
     const size_t ncopy = bytes < (size_t)cap ? bytes : (size_t)cap;
     if (cudaMemcpyAsync(dst, src, ncopy, cudaMemcpyDeviceToDevice, (cudaStream_t)stream) != cudaSuccess) {
       set_error("debug_fetch: copy failed"); return GSR_ERR_CUDA;

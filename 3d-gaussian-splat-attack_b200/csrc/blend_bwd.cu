@@ -23,7 +23,13 @@
 namespace gsr {
 namespace {
 
-constexpr int GRP = 16;          // kept entries per phase-2 sweep
+#ifndef GSR_BWD_GRP
+#define GSR_BWD_GRP 16
+#endif
+#ifndef GSR_BWD_MINBLOCKS
+#define GSR_BWD_MINBLOCKS 4
+#endif
+constexpr int GRP = GSR_BWD_GRP;  // kept entries per phase-2 sweep (8 or 16); each lane then sweeps GRP pixels
 constexpr int PANEL_STRIDE = 33; // float2 row stride of the panel (bank-conflict-free in both phases)
 constexpr int NWARP = TILE_PIX / 32;
 
@@ -67,24 +73,24 @@ __device__ __forceinline__ float fast_rcp(float x) {
   return r;
 }
 
-// Phase 2: lane (e = lane & 15, h = lane >> 4) sums, over pixel lanes h*16 .. h*16+15, the 9 per-Gaussian
-// quantities of group entry e; the two halves are joined with one shuffle per value and lanes < ng issue the REDs.
+// Phase 2: lane (e = lane % GRP, h = lane / GRP) sums, over pixel lanes h*GRP .. h*GRP+GRP-1, the 9 per-Gaussian
+// quantities of group entry e; the 32/GRP partial sums are joined with shuffles and lanes < ng issue the REDs.
 __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int lane, float wx0f, float wy0f,
                                             float* __restrict__ accum) {
   __syncwarp();
-  const int e = lane & (GRP - 1), h = lane >> 4;
+  const int e = lane & (GRP - 1), h = lane / GRP;
   float cx = 0.f, cy = 0.f;
   uint32_t g = 0;
   if (e < ng) {
     const int j = Wp.gj[e];
     cx = M.S.a[j].x; cy = M.S.a[j].y; g = M.id[j];
   }
-  const float wyh = wy0f + (float)(2 * h);
-  const float2* row = &Wp.panel[e][h * 16];
-  const float4* pix = &Wp.pix[h * 16];
+  const float wyh = wy0f + (float)(h * (GRP / 8));
+  const float2* row = &Wp.panel[e][h * GRP];
+  const float4* pix = &Wp.pix[h * GRP];
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, m0 = 0.f, m1 = 0.f, m2 = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f;
 #pragma unroll
-  for (int i = 0; i < 16; i++) {
+  for (int i = 0; i < GRP; i++) {
     const float2 pr = row[i];
     const float4 dp = pix[i];
     const float dx = cx - (wx0f + (float)(i & 7)), dy = cy - (wyh + (float)(i >> 3));
@@ -93,11 +99,14 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
     m0 += pr.y; m1 += wx; m2 += wy;
     mxx = fmaf(wx, dx, mxx); mxy = fmaf(wx, dy, mxy); myy = fmaf(wy, dy, myy);
   }
-  s0 += __shfl_xor_sync(0xffffffffu, s0, 16); s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-  s2 += __shfl_xor_sync(0xffffffffu, s2, 16); m0 += __shfl_xor_sync(0xffffffffu, m0, 16);
-  m1 += __shfl_xor_sync(0xffffffffu, m1, 16); m2 += __shfl_xor_sync(0xffffffffu, m2, 16);
-  mxx += __shfl_xor_sync(0xffffffffu, mxx, 16); mxy += __shfl_xor_sync(0xffffffffu, mxy, 16);
-  myy += __shfl_xor_sync(0xffffffffu, myy, 16);
+#pragma unroll
+  for (int off = GRP; off < 32; off <<= 1) {
+    s0 += __shfl_xor_sync(0xffffffffu, s0, off); s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, off); m0 += __shfl_xor_sync(0xffffffffu, m0, off);
+    m1 += __shfl_xor_sync(0xffffffffu, m1, off); m2 += __shfl_xor_sync(0xffffffffu, m2, off);
+    mxx += __shfl_xor_sync(0xffffffffu, mxx, off); mxy += __shfl_xor_sync(0xffffffffu, mxy, off);
+    myy += __shfl_xor_sync(0xffffffffu, myy, off);
+  }
   if (lane < ng) {
     float* dst = accum + (size_t)g * 12;
     atomicAdd(dst + 0, s0); atomicAdd(dst + 1, s1); atomicAdd(dst + 2, s2);
@@ -109,7 +118,7 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
 }
 
 template <int K>
-__global__ void __launch_bounds__(TILE_PIX)
+__global__ void __launch_bounds__(TILE_PIX, (K > 0 ? 1 : GSR_BWD_MINBLOCKS))
 blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                  const float* __restrict__ bg, const float2* __restrict__ means2D,
                  const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb_thr,

@@ -61,6 +61,8 @@ struct Geom {
   uint32_t* tiles_touched; // [P]
   uint32_t* point_offsets; // [P]  inclusive prefix sum of tiles_touched
   ushort4* rects;          // [P]  (x0, y0, x1, y1) tile rect (auxiliary.h:46-56)
+  uint32_t* perm;          // [P]  Gaussian indices in (depth bits, index) order
+  uint32_t* offsets_sorted;// [P]  inclusive prefix sum of tiles_touched[perm[.]]
   size_t bytes;
   Geom(void* buf, int P) {
     Carver c(buf);
@@ -74,6 +76,8 @@ struct Geom {
     tiles_touched = c.take<uint32_t>(n);
     point_offsets = c.take<uint32_t>(n);
     rects = c.take<ushort4>(n);
+    perm = c.take<uint32_t>(n);
+    offsets_sorted = c.take<uint32_t>(n);
     bytes = c.off;
   }
 };
@@ -119,30 +123,45 @@ struct SortTemp {
 };
 
 // Reusable scratch (not needed after the call that used it returns).
+//
+// Binning works in two stable sorts instead of the reference's one sort of 64-bit (tile | depth) keys
+// (rasterizer_impl.cu:289-308): Gaussians are first ordered by (depth bits, index) -- a 32-bit sort of P
+// items -- then (tile, Gaussian) pairs are emitted in that order and stably sorted by tile id alone.
+// Within a tile the result is ordered by (depth bits, index), i.e. exactly the reference's order.
 constexpr int PRE_THREADS = 256;  // Gaussians per preprocess block
+constexpr int SCAN_ITEMS = 1024;  // Gaussians per block of the sorted-order scan
 struct Scratch {
-  unsigned long long* scan_status;  // [pre_blocks] look-back words of the fused prefix sum
-  uint32_t* scan_ticket;            // [64]
-  uint32_t* flags;                  // [64] flags[0] = prefiltered violation
-  uint64_t* keys_a;                 // [L] unsorted keys
-  uint64_t* keys_b;                 // [L] sorted keys
-  uint32_t* vals_a;                 // [L] unsorted values
+  unsigned long long* scan_status;   // [pre_blocks] look-back words of the fused prefix sum
+  unsigned long long* scan2_status;  // [scan_blocks] look-back words of the sorted-order prefix sum
+  uint32_t* scan_ticket;             // [64] ([0] preprocess, [1] sorted-order scan)
+  uint32_t* flags;                   // [64] flags[0] = prefiltered violation
+  float* accum;                      // [P][12] backward accumulators
+  uint32_t* dkeys_a;                 // [P] depth keys (ping)
+  uint32_t* dkeys_b;                 // [P] depth keys (pong)
+  uint32_t* dvals_b;                 // [P] pong of geom.perm
+  uint32_t* tkeys_a;                 // [L] tile ids (ping)
+  uint32_t* tkeys_b;                 // [L] tile ids (pong)
+  uint32_t* vals_a;                  // [L] partner of point_list
   void* sort_temp;
-  float* accum;                     // [P][12] backward accumulators
   size_t scan_zero_bytes;
   size_t bytes;
   Scratch(void* buf, int P, int64_t L) {
     Carver c(buf);
     size_t pre_blocks = ((size_t)P + PRE_THREADS - 1) / PRE_THREADS;
+    size_t scan_blocks = ((size_t)P + SCAN_ITEMS - 1) / SCAN_ITEMS;
     scan_status = c.take<unsigned long long>(pre_blocks + 1);
+    scan2_status = c.take<unsigned long long>(scan_blocks + 1);
     scan_ticket = c.take<uint32_t>(64);
     flags = c.take<uint32_t>(64);
     scan_zero_bytes = c.off;
     accum = c.take<float>((size_t)P * 12);
-    keys_a = c.take<uint64_t>((size_t)L);
-    keys_b = c.take<uint64_t>((size_t)L);
+    dkeys_a = c.take<uint32_t>((size_t)P);
+    dkeys_b = c.take<uint32_t>((size_t)P);
+    dvals_b = c.take<uint32_t>((size_t)P);
+    tkeys_a = c.take<uint32_t>((size_t)L);
+    tkeys_b = c.take<uint32_t>((size_t)L);
     vals_a = c.take<uint32_t>((size_t)L);
-    sort_temp = c.take<char>(SortTemp(nullptr, L).bytes);
+    sort_temp = c.take<char>(SortTemp(nullptr, L > P ? L : (int64_t)P).bytes);
     bytes = c.off;
   }
 };
@@ -150,11 +169,15 @@ struct Scratch {
 // ---- stage launchers (each returns a gsr_status) ---------------------------------------------
 int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch& s, uint32_t* num_rendered_dev,
                           cudaStream_t st);
-int launch_duplicate_keys(int P, const Geom& g, const int32_t* radii, int gx, uint64_t* keys, uint32_t* vals,
-                          cudaStream_t st);
+int launch_sorted_scan(int P, const Geom& g, Scratch& s, cudaStream_t st);
+int launch_duplicate_tiles(int P, const Geom& g, int gx, uint32_t* tile_keys, uint32_t* vals, cudaStream_t st);
+int launch_rebuild_keys(int64_t L, const uint32_t* tile_keys, const uint32_t* point_list, const float* depths,
+                        uint64_t* keys_out, cudaStream_t st);
 int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
                                int end_bit, void* temp, int* passes_out, cudaStream_t st);
-int launch_tile_ranges(int64_t L, const uint64_t* keys_sorted, uint2* ranges, int tiles, cudaStream_t st);
+int launch_sort_pairs_pingpong_u32(uint32_t* keys0, uint32_t* vals0, uint32_t* keys1, uint32_t* vals1, int64_t n,
+                                   int end_bit, void* temp, int* passes_out, cudaStream_t st);
+int launch_tile_ranges(int64_t L, const uint32_t* tile_keys_sorted, uint2* ranges, int tiles, cudaStream_t st);
 int launch_blend_fwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
                      float* out_color, float* out_objects, cudaStream_t st);
 int launch_blend_bwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,

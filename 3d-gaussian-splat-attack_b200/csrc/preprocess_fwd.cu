@@ -175,7 +175,8 @@ __device__ __forceinline__ unsigned long long pack_status(uint32_t flag, uint32_
 
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, unsigned long long* scan_status,
-                      uint32_t* scan_ticket, uint32_t* flags, uint32_t* num_rendered, int nblocks) {
+                      uint32_t* scan_ticket, uint32_t* flags, uint32_t* num_rendered, uint32_t* __restrict__ dkeys,
+                      int nblocks) {
   __shared__ Cam cam;
   __shared__ uint32_t s_tile, s_warp_sums[PRE_THREADS / 32], s_prefix;
   const int tid = threadIdx.x;
@@ -270,6 +271,10 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, unsign
     radii[idx] = radius;
     g.tiles_touched[idx] = touched;
     g.rects[idx] = rect;
+    // input of the (depth bits, index) ordering: rendered Gaussians sort by their depth bits (positive floats
+    // order like unsigned integers, as in the reference's keys), the others go last
+    dkeys[idx] = touched ? __float_as_uint(depth) : 0xffffffffu;
+    g.perm[idx] = (uint32_t)idx;
   }
 
   // ---- fused inclusive prefix sum over tiles_touched (decoupled look-back across blocks) ----
@@ -334,7 +339,7 @@ int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch
   const int nblocks = (in.P + PRE_THREADS - 1) / PRE_THREADS;
   GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_status, 0, s.scan_zero_bytes, st));
   preprocess_fwd_kernel<<<nblocks, PRE_THREADS, 0, st>>>(in, g, radii, s.scan_status, s.scan_ticket, s.flags,
-                                                          num_rendered_dev, nblocks);
+                                                          num_rendered_dev, s.dkeys_a, nblocks);
   GSR_LAUNCH_CHECK("preprocess_fwd_kernel");
   return GSR_OK;
 }

@@ -20,15 +20,16 @@ namespace {
 constexpr uint32_t ST_AGG = 1u << 30, ST_PREFIX = 1u << 31, ST_MASK = (1u << 30) - 1;
 constexpr int NWARPS = SORT_THREADS / 32;
 
+template <typename KeyT>
 __global__ void __launch_bounds__(256)
-sort_histogram_kernel(const uint64_t* __restrict__ keys, int64_t n, int passes, int end_bit,
+sort_histogram_kernel(const KeyT* __restrict__ keys, int64_t n, int passes, int end_bit,
                       uint32_t* __restrict__ hist) {
   __shared__ uint32_t sh[SORT_MAX_PASSES * 256];
   for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) sh[i] = 0;
   __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const uint64_t k = keys[i];
+    const KeyT k = keys[i];
     for (int p = 0; p < passes; p++) {
       const int shift = 8 * p, nb = min(8, end_bit - shift);
       atomicAdd(&sh[p * 256 + (uint32_t)((k >> shift) & ((1u << nb) - 1))], 1u);
@@ -58,8 +59,9 @@ __global__ void sort_scan_hist_kernel(uint32_t* hist, int passes) {
   for (int k = 0; k < 8; k++) { h[lane * 8 + k] = run; run += v[k]; }
 }
 
+template <typename KeyT>
 struct PassSmem {
-  uint64_t keys[SORT_TILE];
+  KeyT keys[SORT_TILE];
   uint32_t vals[SORT_TILE];
   uint32_t warp_hist[NWARPS][256];
   uint32_t digit_off[256];   // exclusive offset of each digit inside the sorted tile
@@ -68,13 +70,14 @@ struct PassSmem {
   uint32_t tile;
 };
 
+template <typename KeyT>
 __global__ void __launch_bounds__(SORT_THREADS)
-onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
+onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, int64_t n, int shift,
                      uint32_t digit_mask, const uint32_t* __restrict__ digit_base, uint32_t* status,
                      uint32_t* ticket) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  PassSmem& S = *reinterpret_cast<PassSmem*>(smem_raw);
+  PassSmem<KeyT>& S = *reinterpret_cast<PassSmem<KeyT>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) S.tile = atomicAdd(ticket, 1u);
 #pragma unroll
@@ -85,14 +88,14 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict_
   const int tile_n = (int)min((int64_t)SORT_TILE, n - tile_base);
 
   // warp-striped load: warp w owns tile items [w*512, (w+1)*512), lane-interleaved
-  uint64_t key[SORT_ITEMS];
+  KeyT key[SORT_ITEMS];
   uint32_t val[SORT_ITEMS], rank[SORT_ITEMS];
   const int wbase = warp * (32 * SORT_ITEMS) + lane;
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; i++) {
     const int t = wbase + i * 32;
     if (t < tile_n) { key[i] = keys_in[tile_base + t]; val[i] = vals_in[tile_base + t]; }
-    else { key[i] = ~0ull; val[i] = 0; }
+    else { key[i] = (KeyT)~(KeyT)0; val[i] = 0; }
   }
 
   // stable per-warp ranking
@@ -166,7 +169,7 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict_
   __syncthreads();
   // coalesced per-digit runs
   for (int s = tid; s < tile_n; s += SORT_THREADS) {
-    const uint64_t k = S.keys[s];
+    const KeyT k = S.keys[s];
     const uint32_t d = (uint32_t)(k >> shift) & digit_mask;
     const int64_t dst = (int64_t)(uint32_t)(S.global_base[d] + s);
     keys_out[dst] = k;
@@ -178,35 +181,47 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict_
 
 // Sorts in place across two buffer pairs: pass p reads pair (p & 1) and writes the other; the
 // result is in pair (passes & 1).  Returns the pass count through *passes_out.
-int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
-                               int end_bit, void* temp, int* passes_out, cudaStream_t st) {
+template <typename KeyT>
+static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32_t* vals1, int64_t n, int end_bit,
+                               void* temp, int* passes_out, cudaStream_t st) {
   const int passes = (end_bit + 7) / 8;
   if (passes_out) *passes_out = passes;
-  if (passes < 1 || passes > SORT_MAX_PASSES) { set_error("sort: end_bit %d out of range", end_bit); return GSR_ERR_INVALID; }
+  if (passes < 1 || passes > (int)sizeof(KeyT) || passes > SORT_MAX_PASSES) {
+    set_error("sort: end_bit %d out of range", end_bit); return GSR_ERR_INVALID;
+  }
   if (n >= (int64_t)ST_MASK) { set_error("sort: %lld pairs exceed the 2^30 limit", (long long)n); return GSR_ERR_INVALID; }
   if (n == 0) return GSR_OK;
   SortTemp T(temp, n);
   GSR_CUDA_CHECK(cudaMemsetAsync(temp, 0, T.zero_bytes, st));
   const int hist_blocks = (int)min((int64_t)148 * 8, (n + 2047) / 2048);
-  sort_histogram_kernel<<<hist_blocks, 256, 0, st>>>(keys0, n, passes, end_bit, T.hist);
+  sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys0, n, passes, end_bit, T.hist);
   GSR_LAUNCH_CHECK("sort_histogram_kernel");
   sort_scan_hist_kernel<<<1, 32 * SORT_MAX_PASSES, 0, st>>>(T.hist, passes);
   GSR_LAUNCH_CHECK("sort_scan_hist_kernel");
-  GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(PassSmem)));
+  GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(PassSmem<KeyT>)));
   const int64_t tiles = sort_tiles(n);
   for (int p = 0; p < passes; p++) {
     const int shift = 8 * p, nb = end_bit - shift < 8 ? end_bit - shift : 8;
-    const uint64_t* kin = (p & 1) ? keys1 : keys0;
-    uint64_t* kout = (p & 1) ? keys0 : keys1;
+    const KeyT* kin = (p & 1) ? keys1 : keys0;
+    KeyT* kout = (p & 1) ? keys0 : keys1;
     const uint32_t* vin = (p & 1) ? vals1 : vals0;
     uint32_t* vout = (p & 1) ? vals0 : vals1;
-    onesweep_pass_kernel<<<(unsigned)tiles, SORT_THREADS, sizeof(PassSmem), st>>>(
+    onesweep_pass_kernel<KeyT><<<(unsigned)tiles, SORT_THREADS, sizeof(PassSmem<KeyT>), st>>>(
         kin, kout, vin, vout, n, shift, (1u << nb) - 1, T.hist + p * 256, T.status + (size_t)p * tiles * 256,
         T.tickets + p);
     GSR_LAUNCH_CHECK("onesweep_pass_kernel");
   }
   return GSR_OK;
+}
+
+int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
+                               int end_bit, void* temp, int* passes_out, cudaStream_t st) {
+  return sort_pairs_pingpong<uint64_t>(keys0, vals0, keys1, vals1, n, end_bit, temp, passes_out, st);
+}
+int launch_sort_pairs_pingpong_u32(uint32_t* keys0, uint32_t* vals0, uint32_t* keys1, uint32_t* vals1, int64_t n,
+                                   int end_bit, void* temp, int* passes_out, cudaStream_t st) {
+  return sort_pairs_pingpong<uint32_t>(keys0, vals0, keys1, vals1, n, end_bit, temp, passes_out, st);
 }
 
 }  // namespace gsr

@@ -9,7 +9,7 @@ import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
-LIB_PATH = os.path.join(_ROOT, "lib", "libgsr_b200.so")
+LIB_PATH = os.environ.get("GSR_B200_LIB") or os.path.join(_ROOT, "lib", "libgsr_b200.so")  # override: kernel experiments
 CSRC_DIR = os.path.join(_ROOT, "csrc")
 
 GSR_OK, GSR_ERR_INVALID, GSR_ERR_CUDA, GSR_ERR_CAPACITY, GSR_ERR_PREFILTERED = 0, -1, -2, -3, -4
@@ -51,7 +51,7 @@ EXPORTS = {
     "gsr_launch_count": (C.c_int64, [C.c_int]),
     "gsr_debug_counters": (C.c_int, [C.c_void_p, C.c_int]),
     "gsr_debug_fetch": (C.c_int64, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
-                                    C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
 }
 
 STAGES = ("preprocess_fwd", "duplicate_keys", "sort", "tile_ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")

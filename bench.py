@@ -280,9 +280,9 @@ def fetch_u32(torch, wl, name):
     lib, fn = _abi.lib(), wl.last_fn
     geom, image = fn.saved_tensors[9], fn.saved_tensors[11]
     pv = lambda t: C.c_void_p(t.data_ptr())
-    n = lib.gsr_debug_fetch(name.encode(), wl.P, wl.W, wl.H, fn.num_rendered, pv(geom), pv(image), None, None, 0, None)
+    n = lib.gsr_debug_fetch(name.encode(), wl.P, wl.W, wl.H, fn.num_rendered, pv(geom), pv(image), None, None, None, 0, None)
     buf = torch.empty(int(n), dtype=torch.uint8, device=wl.dev)
-    lib.gsr_debug_fetch(name.encode(), wl.P, wl.W, wl.H, fn.num_rendered, pv(geom), pv(image), None, pv(buf), n, None)
+    lib.gsr_debug_fetch(name.encode(), wl.P, wl.W, wl.H, fn.num_rendered, pv(geom), pv(image), None, None, pv(buf), n, None)
     torch.cuda.synchronize()
     return buf.cpu().numpy().view(np.uint32)
 
@@ -322,9 +322,9 @@ def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
     fp32_instr = {"blend_fwd": 20, "blend_bwd": 45}
     fp32_peak = 148 * 128 * sm_max_mhz * 1e6  # lane-instructions / s
     out, total = {}, 0.0
+    views = max(int(calls[_abi.STAGES.index("blend_fwd")]), 1)
     for i, name in enumerate(_abi.STAGES):
-        n = max(int(calls[i]), 1)
-        avg = float(ms[i]) / n
+        avg = float(ms[i]) / views  # a stage may be recorded more than once per view (two sorts)
         total += avg
         e = {"ms": avg, "calls": int(calls[i]), "alg_bytes": int(alg[name]),
              "hbm_gbs": alg[name] / (avg * 1e-3) / 1e9 if avg > 0 else None}

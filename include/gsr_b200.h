@@ -115,10 +115,14 @@ int gsr_sort_pairs_u64(const uint64_t* keys_in, uint64_t* keys_out, const uint32
 
 /* Copies internal arrays of a finished forward out for inspection. name is one of: "depths",
  * "means2D", "cov3D", "conic_opacity", "rgb", "clamped", "tiles_touched", "point_offsets", "rects",
- * "final_T", "n_contrib", "ranges", "keys_unsorted", "vals_unsorted", "keys_sorted".
- * Returns the byte count (copying min(count, cap) bytes into dst, a device pointer), <0 on error. */
+ * "perm", "offsets_sorted", "final_T", "n_contrib", "ranges", "tiles_sorted", "keys_sorted".
+ * "keys_sorted" is the reference's sorted 64-bit key list (tile << 32 | depth bits,
+ * rasterizer_impl.cu:303-308), rebuilt from the sorted tile ids, point_list and depths (needs
+ * scratch, point_list and cap >= 8 L).  Returns the byte count (copying min(count, cap) bytes
+ * into dst, a device pointer), <0 on error. */
 int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64_t L, const void* geom,
-                        const void* image, const void* scratch, void* dst, int64_t cap, void* stream);
+                        const void* image, const void* scratch, const uint32_t* point_list, void* dst,
+                        int64_t cap, void* stream);
 
 /* ---- measurement hooks (bench.py): per-stage CUDA-event timing on the launching stream and a
  *      count of kernel launches.  Stage order: preprocess_fwd, duplicate_keys, sort, tile_ranges,

@@ -50,15 +50,16 @@ def scene_tensors(scene, device="cuda", requires_grad=True):
     return out
 
 
-def gsr_fetch(name, dtype, P, W, H, L, geom, image, scratch):
+def gsr_fetch(name, dtype, P, W, H, L, geom, image, scratch, point_list=None):
     """Copy an internal array of the product's last forward out (gsr_debug_fetch)."""
     from diff_gaussian_rasterization import _abi
     lib = _abi.lib()
     p = lambda t: C.c_void_p(t.data_ptr()) if t is not None and t.numel() else None
-    n = lib.gsr_debug_fetch(name.encode(), P, W, H, L, p(geom), p(image), p(scratch), None, 0, None)
+    n = lib.gsr_debug_fetch(name.encode(), P, W, H, L, p(geom), p(image), p(scratch), p(point_list), None, 0, None)
     assert n >= 0, _abi.last_error()
     buf = torch.empty(max(int(n), 1), dtype=torch.uint8, device="cuda")
-    lib.gsr_debug_fetch(name.encode(), P, W, H, L, p(geom), p(image), p(scratch), p(buf), n, None)
+    r = lib.gsr_debug_fetch(name.encode(), P, W, H, L, p(geom), p(image), p(scratch), p(point_list), p(buf), n, None)
+    assert r >= 0, _abi.last_error()
     torch.cuda.synchronize()
     return buf[:n].cpu().numpy().view(dtype)
 
@@ -101,7 +102,7 @@ def run_gsr(scene, grad=True, fetch=True, obj=None, bg=None, colors_precomp=None
                          ("conic_opacity", np.float32), ("rgb", np.float32), ("clamped", np.uint8),
                          ("tiles_touched", np.uint32), ("point_offsets", np.uint32), ("final_T", np.float32),
                          ("n_contrib", np.uint32), ("ranges", np.uint32), ("keys_sorted", np.uint64)):
-            res[name] = gsr_fetch(name, dt, P, W, H, L, geom, image, scratch)
+            res[name] = gsr_fetch(name, dt, P, W, H, L, geom, image, scratch, point_list)
         res["rgb"] = res["rgb"].reshape(P, 4)[:, :3].copy()
         res["point_list"] = point_list[:L].cpu().numpy().view(np.uint32)
     if grad:

@@ -61,7 +61,7 @@ def test_buffer_size_queries_are_monotone_and_aligned():
     assert lib.gsr_image_bytes(1920, 1080) >= 8 * 1920 * 1080 + 8 * 8160
     s0 = lib.gsr_scratch_bytes(1000, 0, 64, 64)
     s1 = lib.gsr_scratch_bytes(1000, 100_000, 64, 64)
-    assert s1 - s0 >= 20 * 100_000
+    assert s1 - s0 >= 12 * 100_000
     assert lib.gsr_sort_temp_bytes(1 << 20) >= 12 * (1 << 20)
 
 
