@@ -70,6 +70,14 @@ static int debug_sync(const gsr_inputs* in, cudaStream_t st, const char* stage) 
 }
 #define GSR_TRY(x) do { int _r = (x); if (_r != GSR_OK) return _r; } while (0)
 
+// Publishes the duplicate count to pinned (device-mapped) host memory with a store instead of a D2H memcpy:
+// a memcpy would queue on the device-to-host copy engine behind any large transfer another stream has in
+// flight (pipeline.HostStepPipeline drains 236 MB of gradients while the next step's forward needs this word).
+__global__ void publish_count_kernel(const uint32_t* __restrict__ dev, volatile uint32_t* host) {
+  *host = *dev;
+  __threadfence_system();
+}
+
 }  // namespace gsr
 
 using namespace gsr;
@@ -127,8 +135,10 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   GSR_TRY(debug_sync(in, st, "depth_sort"));
   { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, st)); }
   GSR_TRY(debug_sync(in, st, "sorted_scan"));
-  if (num_rendered_host)
-    GSR_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, 4, cudaMemcpyDeviceToHost, st));
+  if (num_rendered_host) {
+    publish_count_kernel<<<1, 1, 0, st>>>(num_rendered_dev, num_rendered_host);
+    GSR_LAUNCH_CHECK("publish_count_kernel");
+  }
   if (in->prefiltered) {
     uint32_t flag = 0;
     GSR_CUDA_CHECK(cudaMemcpyAsync(&flag, s.flags, 4, cudaMemcpyDeviceToHost, st));
@@ -179,20 +189,22 @@ int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* ra
   return GSR_OK;
 }
 
-int gsr_backward(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, const uint32_t* point_list,
-                 const void* image, void* scratch, size_t scratch_bytes, const float* dL_dpix, const float* dL_dobjpix,
-                 float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
-                 float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dobj, void* stream) {
+static int backward_impl(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
+                         const uint32_t* point_list, const void* image, void* scratch, size_t scratch_bytes,
+                         const float* dL_dpix, const float* dL_dobjpix, float* dL_dmean2D, float* dL_dopacity,
+                         float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
+                         float* dL_drot, float* dL_dobj, bool accumulate, void* stream) {
   GSR_TRY(check_inputs(in));
   cudaStream_t st = (cudaStream_t)stream;
   if (in->P == 0) return GSR_OK;
-  if (!geom || !radii || !image || !scratch || !dL_dpix || !dL_dmean2D || !dL_dopacity || !dL_dmean3D ||
+  if (!geom || !radii || !image || !scratch || !dL_dpix || (!dL_dmean2D && !accumulate) || !dL_dopacity || !dL_dmean3D ||
       (L > 0 && !point_list)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
   if (in->shs && !dL_dsh) { set_error("dL_dsh is NULL but shs given"); return GSR_ERR_INVALID; }
   if (in->scales && (!dL_dscale || !dL_drot)) { set_error("dL_dscale/dL_drot NULL but scales given"); return GSR_ERR_INVALID; }
   if (in->cov3D_precomp && !dL_dcov3D) { set_error("dL_dcov3D NULL but cov3D_precomp given"); return GSR_ERR_INVALID; }
   if (in->colors_precomp && !dL_dcolor) { set_error("dL_dcolor NULL but colors_precomp given"); return GSR_ERR_INVALID; }
   if (in->K > 0 && (!dL_dobjpix || !dL_dobj)) { set_error("object gradients NULL but K>0"); return GSR_ERR_INVALID; }
+  if (accumulate && in->K > 0) { set_error("backward_accumulate: object channels are not supported"); return GSR_ERR_INVALID; }
   if (scratch_bytes < Scratch(nullptr, in->P, 0).bytes) { set_error("scratch too small"); return GSR_ERR_CAPACITY; }
   Geom g(const_cast<void*>(geom), in->P);
   Image im(const_cast<void*>(image), in->W, in->H);
@@ -202,9 +214,26 @@ int gsr_backward(const gsr_inputs* in, const void* geom, const int32_t* radii, i
   { StageScope ps(ST_PREPROCESS_BWD, st);
     GSR_TRY(launch_preprocess_bwd(*in, g, radii, s.accum, dL_dmean2D, dL_dopacity, in->colors_precomp ? dL_dcolor : nullptr,
                                   dL_dmean3D, in->cov3D_precomp ? dL_dcov3D : nullptr, in->shs ? dL_dsh : nullptr,
-                                  in->scales ? dL_dscale : nullptr, in->scales ? dL_drot : nullptr, st)); }
+                                  in->scales ? dL_dscale : nullptr, in->scales ? dL_drot : nullptr, accumulate, st)); }
   GSR_TRY(debug_sync(in, st, "preprocess_bwd"));
   return GSR_OK;
+}
+
+int gsr_backward(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, const uint32_t* point_list,
+                 const void* image, void* scratch, size_t scratch_bytes, const float* dL_dpix, const float* dL_dobjpix,
+                 float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dobj, void* stream) {
+  return backward_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, dL_dpix, dL_dobjpix, dL_dmean2D,
+                       dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dobj, false, stream);
+}
+
+int gsr_backward_accumulate(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
+                            const uint32_t* point_list, const void* image, void* scratch, size_t scratch_bytes,
+                            const float* dL_dpix, float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor,
+                            float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                            void* stream) {
+  return backward_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, dL_dpix, nullptr, dL_dmean2D,
+                       dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, true, stream);
 }
 
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* /*projmatrix*/,

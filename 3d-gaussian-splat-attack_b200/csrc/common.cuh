@@ -184,7 +184,8 @@ int launch_blend_bwd(const gsr_inputs& in, const Geom& g, const Image& im, const
                      const float* dL_dpix, const float* dL_dobjpix, float* accum, float* dL_dobj, cudaStream_t st);
 int launch_preprocess_bwd(const gsr_inputs& in, const Geom& g, const int32_t* radii, const float* accum,
                           float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
-                          float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, cudaStream_t st);
+                          float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, bool accumulate,
+                          cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 
 uint32_t higher_msb(uint32_t n);

@@ -59,6 +59,15 @@ __device__ __forceinline__ V3 sh_backward(int deg, float x, float y, float z, V3
   return V3{dot(gx, dRGB), dot(gy, dRGB), dot(gz, dRGB)};
 }
 
+__device__ __forceinline__ void red_add4(float4* p, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// ACC = false: every output row is written (zeros for Gaussians that were not rendered).
+// ACC = true : the gradients of this view are ADDED to the caller's buffers (a multi-view step accumulates
+//              into one flat bucket without per-view temporaries); rows of unrendered Gaussians are untouched,
+//              dL_dmean2D may be NULL.
+template <bool ACC>
 __global__ void __launch_bounds__(256)
 preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, const float* __restrict__ accum,
                       float* __restrict__ dL_dmean2D, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor,
@@ -71,6 +80,7 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= in.P) return;
   const bool live = radii[idx] > 0;
+  if (ACC && !live) return;
   const int M = in.M;
 
   float4 a0 = make_float4(0, 0, 0, 0), a1 = a0;
@@ -88,9 +98,15 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
     a1.x = op * (0.5f * in.H) * (-co.z * m2 - co.y * m1);
     a1.y *= -0.5f * op; a1.z *= -0.5f * op; a1.w *= -0.5f * op;
   }
-  dL_dmean2D[3 * (size_t)idx] = a0.w; dL_dmean2D[3 * (size_t)idx + 1] = a1.x; dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
-  dL_dopacity[idx] = a8;
-  if (dL_dcolor) { dL_dcolor[3 * (size_t)idx] = a0.x; dL_dcolor[3 * (size_t)idx + 1] = a0.y; dL_dcolor[3 * (size_t)idx + 2] = a0.z; }
+  if (ACC) {
+    if (dL_dmean2D) { atomicAdd(dL_dmean2D + 3 * (size_t)idx, a0.w); atomicAdd(dL_dmean2D + 3 * (size_t)idx + 1, a1.x); }
+    atomicAdd(dL_dopacity + idx, a8);
+    if (dL_dcolor) { atomicAdd(dL_dcolor + 3 * (size_t)idx, a0.x); atomicAdd(dL_dcolor + 3 * (size_t)idx + 1, a0.y); atomicAdd(dL_dcolor + 3 * (size_t)idx + 2, a0.z); }
+  } else {
+    dL_dmean2D[3 * (size_t)idx] = a0.w; dL_dmean2D[3 * (size_t)idx + 1] = a1.x; dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+    dL_dopacity[idx] = a8;
+    if (dL_dcolor) { dL_dcolor[3 * (size_t)idx] = a0.x; dL_dcolor[3 * (size_t)idx + 1] = a0.y; dL_dcolor[3 * (size_t)idx + 2] = a0.z; }
+  }
 
   float dmean[3] = {0.f, 0.f, 0.f}, dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float dscale[3] = {0.f, 0.f, 0.f}, drot[4] = {0.f, 0.f, 0.f, 0.f};
@@ -177,14 +193,24 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
         for (int k = 0; k < 48; k++) outv[k] = 0.f;
         ddir = sh_backward(in.D, x, y, z, dRGB, [&](int i) { return V3{shv[3 * i], shv[3 * i + 1], shv[3 * i + 2]}; },
                            [&](int i, float w) { outv[3 * i] = w * dRGB.x; outv[3 * i + 1] = w * dRGB.y; outv[3 * i + 2] = w * dRGB.z; });
+        const int nq = ACC ? (3 * (in.D + 1) * (in.D + 1) + 3) / 4 : 12;  // ACC: only the active coefficients change
 #pragma unroll
-        for (int k = 0; k < 12; k++) dp[k] = make_float4(outv[4 * k], outv[4 * k + 1], outv[4 * k + 2], outv[4 * k + 3]);
+        for (int k = 0; k < 12; k++) {
+          if (k < nq) {
+            float4 o = make_float4(outv[4 * k], outv[4 * k + 1], outv[4 * k + 2], outv[4 * k + 3]);
+            if (ACC) red_add4(dp + k, o);  // RED.ADD.F32x4: no read round trip through the SM
+            else dp[k] = o;
+          }
+        }
       } else {
         const float* sp = in.shs + (size_t)idx * M * 3;
         float* dp = dL_dsh + (size_t)idx * M * 3;
-        for (int k = 0; k < 3 * M; k++) dp[k] = 0.f;
+        if (!ACC) for (int k = 0; k < 3 * M; k++) dp[k] = 0.f;
         ddir = sh_backward(in.D, x, y, z, dRGB, [&](int i) { return V3{sp[3 * i], sp[3 * i + 1], sp[3 * i + 2]}; },
-                           [&](int i, float w) { dp[3 * i] = w * dRGB.x; dp[3 * i + 1] = w * dRGB.y; dp[3 * i + 2] = w * dRGB.z; });
+                           [&](int i, float w) {
+                             if (ACC) { atomicAdd(dp + 3 * i, w * dRGB.x); atomicAdd(dp + 3 * i + 1, w * dRGB.y); atomicAdd(dp + 3 * i + 2, w * dRGB.z); }
+                             else { dp[3 * i] = w * dRGB.x; dp[3 * i + 1] = w * dRGB.y; dp[3 * i + 2] = w * dRGB.z; }
+                           });
       }
       // d(normalised direction)/d(mean)
       const float inv32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
@@ -233,6 +259,20 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
       for (int k = 0; k < 3 * M; k++) dp[k] = 0.f;
     }
   }
+  if (ACC) {
+#pragma unroll
+    for (int k = 0; k < 3; k++) atomicAdd(dL_dmean3D + 3 * (size_t)idx + k, dmean[k]);
+    if (dL_dcov3D) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) atomicAdd(dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
+    }
+    if (dL_dscale) {
+#pragma unroll
+      for (int k = 0; k < 3; k++) atomicAdd(dL_dscale + 3 * (size_t)idx + k, dscale[k]);
+      red_add4(reinterpret_cast<float4*>(dL_drot) + idx, make_float4(drot[0], drot[1], drot[2], drot[3]));
+    }
+    return;
+  }
 #pragma unroll
   for (int k = 0; k < 3; k++) dL_dmean3D[3 * (size_t)idx + k] = dmean[k];
   if (dL_dcov3D) {
@@ -250,9 +290,14 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
 
 int launch_preprocess_bwd(const gsr_inputs& in, const Geom& g, const int32_t* radii, const float* accum,
                           float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
-                          float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, cudaStream_t st) {
-  preprocess_bwd_kernel<<<(in.P + 255) / 256, 256, 0, st>>>(in, g, radii, accum, dL_dmean2D, dL_dopacity, dL_dcolor,
-                                                             dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
+                          float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, bool accumulate,
+                          cudaStream_t st) {
+  if (accumulate)
+    preprocess_bwd_kernel<true><<<(in.P + 255) / 256, 256, 0, st>>>(in, g, radii, accum, dL_dmean2D, dL_dopacity, dL_dcolor,
+                                                                     dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
+  else
+    preprocess_bwd_kernel<false><<<(in.P + 255) / 256, 256, 0, st>>>(in, g, radii, accum, dL_dmean2D, dL_dopacity, dL_dcolor,
+                                                                      dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
   GSR_LAUNCH_CHECK("preprocess_bwd_kernel");
   return GSR_OK;
 }

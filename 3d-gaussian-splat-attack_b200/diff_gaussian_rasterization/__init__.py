@@ -92,6 +92,47 @@ def _make_inputs(rs, P, M, K, means3D, sh, colors_precomp, opacities, scales, ro
     return inp
 
 
+def _run_forward(rs, P, M, K, want_obj, means3D_c, sh_c, col_c, op_c, sc_c, rot_c, cov_c, obj_c):
+    """Both forward phases of one view through the C ABI (Rasterizer::forward, rasterizer_impl.cu:198-336).
+    Returns (color, objects, radii, L, geom, point_list, image); the last three are what backward needs."""
+    dev = means3D_c.device
+    H, W = int(rs.image_height), int(rs.image_width)
+    color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    objects = torch.empty((K, H, W), dtype=torch.float32, device=dev) if want_obj else None
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    L = 0
+    geom = image = point_list = None
+    with torch.cuda.device(dev):
+        lib = _abi.lib()
+        st = _state(dev)
+        stream = torch.cuda.current_stream(dev)
+        sp = C.c_void_p(stream.cuda_stream)
+        keep = []
+        inp = _make_inputs(rs, P, M, K if want_obj else 0, means3D_c, sh_c, col_c, op_c, sc_c, rot_c, cov_c,
+                           obj_c, keep)
+        if P == 0:
+            color.zero_()
+            if want_obj:
+                objects.zero_()
+        else:
+            geom = torch.empty(lib.gsr_geom_bytes(P), dtype=torch.uint8, device=dev)
+            image = torch.empty(lib.gsr_image_bytes(W, H), dtype=torch.uint8, device=dev)
+            scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, 0, W, H))
+            _abi.check(lib.gsr_forward_geometry(C.byref(inp), _ptr(geom), _ptr(radii), _ptr(scratch),
+                                                scratch.numel(), _ptr(st.count_dev),
+                                                C.c_void_p(st.count_host.data_ptr()), sp), "forward_geometry")
+            stream.synchronize()  # the one host sync per view (reference: rasterizer_impl.cu:281)
+            L = int(st.count_host.item()) & 0xFFFFFFFF
+            point_list = torch.empty((max(L, 1),), dtype=torch.int32, device=dev)
+            scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, L, W, H))
+            _abi.check(lib.gsr_forward_render(C.byref(inp), _ptr(geom), _ptr(radii), L, _ptr(point_list),
+                                              _ptr(image), _ptr(scratch), scratch.numel(), _ptr(color),
+                                              _ptr(objects), sp), "forward_render")
+            if rs.debug:
+                stream.synchronize()
+    return color, objects, radii, L, geom, point_list, image
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings, sh_objs=None):
     out = _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
@@ -124,40 +165,9 @@ class _RasterizeGaussians(torch.autograd.Function):
                                               rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix,
                                               rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
                                               rs.sh_degree, rs.campos, rs.prefiltered, rs.debug))
-        color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
-        objects = torch.empty((K, H, W), dtype=torch.float32, device=dev) if want_obj else None
-        radii = torch.empty((P,), dtype=torch.int32, device=dev)
-        L = 0
-        geom = image = point_list = None
         try:
-            with torch.cuda.device(dev):
-                lib = _abi.lib()
-                st = _state(dev)
-                stream = torch.cuda.current_stream(dev)
-                sp = C.c_void_p(stream.cuda_stream)
-                keep = []
-                inp = _make_inputs(rs, P, M, K if want_obj else 0, means3D_c, sh_c, col_c, op_c, sc_c, rot_c, cov_c,
-                                   obj_c, keep)
-                if P == 0:
-                    color.zero_()
-                    if want_obj:
-                        objects.zero_()
-                else:
-                    geom = torch.empty(lib.gsr_geom_bytes(P), dtype=torch.uint8, device=dev)
-                    image = torch.empty(lib.gsr_image_bytes(W, H), dtype=torch.uint8, device=dev)
-                    scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, 0, W, H))
-                    _abi.check(lib.gsr_forward_geometry(C.byref(inp), _ptr(geom), _ptr(radii), _ptr(scratch),
-                                                        scratch.numel(), _ptr(st.count_dev),
-                                                        C.c_void_p(st.count_host.data_ptr()), sp), "forward_geometry")
-                    stream.synchronize()  # the one host sync per view (reference: rasterizer_impl.cu:281)
-                    L = int(st.count_host.item()) & 0xFFFFFFFF
-                    point_list = torch.empty((max(L, 1),), dtype=torch.int32, device=dev)
-                    scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, L, W, H))
-                    _abi.check(lib.gsr_forward_render(C.byref(inp), _ptr(geom), _ptr(radii), L, _ptr(point_list),
-                                                      _ptr(image), _ptr(scratch), scratch.numel(), _ptr(color),
-                                                      _ptr(objects), sp), "forward_render")
-                    if rs.debug:
-                        stream.synchronize()
+            color, objects, radii, L, geom, point_list, image = _run_forward(
+                rs, P, M, K, want_obj, means3D_c, sh_c, col_c, op_c, sc_c, rot_c, cov_c, obj_c)
         except Exception as ex:
             if rs.debug:
                 torch.save(debug_args, "snapshot_fw.dump")

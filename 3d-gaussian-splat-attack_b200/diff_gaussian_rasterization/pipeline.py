@@ -1,0 +1,153 @@
+"""Host-buffer step pipeline: multi-view gradient steps whose inputs and outputs live in HOST memory.
+
+A step = render `n_views` cameras forward + backward against one Gaussian set and return the summed
+attribute gradients (the inner loop of attack.py:463-530 with the detector replaced by a given dL/dimage).
+Inputs per step (pinned host memory): the flat attribute vector [means3D | shs | scales | rotations | opacities]
+(236 B per Gaussian at SH degree 3 -- the same layout as the all-reduce bucket, dist.FlatGradBucket), one
+36-float row per camera (viewmatrix 16, projmatrix 16, campos 3, pad) and one (3,H,W) dL/dimage per camera.
+Output per step: the flat gradient vector in pinned host memory.
+
+Three CUDA streams, two device buffer sets: while step i computes, the copy-in stream already moves step
+i+1's inputs and the copy-out stream drains step i-1's gradients (PCIe is full duplex), so in steady state a
+step costs max(compute, H2D, D2H) instead of their sum.  submit() is software-pipelined by one step because
+the forward has one host sync per view (the duplicate count, as in rasterizer_impl.cu:281): the host thread
+can only queue step i+1's copies before it starts issuing step i's kernels.
+"""
+from typing import List, Optional
+
+import torch
+
+from . import GaussianRasterizationSettings
+from . import views as _views
+
+__all__ = ["HostStepPipeline", "ATTRS"]
+
+# flat layout: name -> floats per Gaussian (SH width is 3*M, filled in per instance)
+ATTRS = ("means3D", "shs", "scales", "rotations", "opacities")
+
+
+class _Slot:
+    def __init__(self, n_param, n_views, H, W, dev, widths, P):
+        f32 = torch.float32
+        self.param = torch.empty(n_param, dtype=f32, device=dev)
+        self.grad = torch.zeros(n_param, dtype=f32, device=dev)
+        self.cam = torch.empty((n_views, 36), dtype=f32, device=dev)
+        self.dL = torch.empty((n_views, 3, H, W), dtype=f32, device=dev)
+        self.p, self.g, off = {}, {}, 0
+        for n, w in widths:
+            shape = (P, w // 3, 3) if n == "shs" else (P, w)
+            self.p[n] = self.param[off:off + P * w].view(shape)
+            self.g[n] = self.grad[off:off + P * w].view(shape)
+            off += P * w
+        self.ev_in = torch.cuda.Event()
+        self.ev_compute = torch.cuda.Event()
+        self.ev_out = torch.cuda.Event()
+        self.pending_out = None  # host gradient tensor the slot's last D2H writes to
+        self.used = False
+
+
+class HostStepPipeline:
+    def __init__(self, P: int, M: int, W: int, H: int, n_views: int, tanfovx: float, tanfovy: float, sh_degree: int,
+                 device, bg: Optional[torch.Tensor] = None, depth: int = 2, group=None):
+        if depth < 1:
+            raise ValueError("depth must be >= 1")
+        self.P, self.M, self.W, self.H, self.n_views = P, M, W, H, n_views
+        self.tanfovx, self.tanfovy, self.sh_degree = float(tanfovx), float(tanfovy), int(sh_degree)
+        self.dev = torch.device(device)
+        self.widths = (("means3D", 3), ("shs", 3 * M), ("scales", 3), ("rotations", 4), ("opacities", 1))
+        self.n_param = P * sum(w for _, w in self.widths)
+        self.bg = torch.zeros(3, device=self.dev) if bg is None else bg.to(self.dev).float()
+        self.slots: List[_Slot] = [_Slot(self.n_param, n_views, H, W, self.dev, self.widths, P) for _ in range(depth)]
+        self.s_in = torch.cuda.Stream(self.dev)
+        self.s_out = torch.cuda.Stream(self.dev)
+        self.group = group
+        self.n_submitted = 0
+        self.staged = None  # slot whose inputs are in flight and whose compute has not been issued yet
+        self.h2d_bytes = 4 * (self.n_param + n_views * 36 + n_views * 3 * H * W)
+        self.d2h_bytes = 4 * self.n_param
+
+    # -- stages ---------------------------------------------------------------------------------------------
+    def _copy_in(self, slot, host_param, host_cam, host_dL):
+        with torch.cuda.stream(self.s_in):
+            if slot.used:
+                self.s_in.wait_event(slot.ev_compute)  # the previous step in this slot has finished reading
+            slot.param.copy_(host_param, non_blocking=True)
+            slot.cam.copy_(host_cam, non_blocking=True)
+            slot.dL.copy_(host_dL, non_blocking=True)
+            slot.ev_in.record(self.s_in)
+
+    def _compute(self, slot):
+        cur = torch.cuda.current_stream(self.dev)
+        cur.wait_event(slot.ev_in)
+        if slot.used:
+            cur.wait_event(slot.ev_out)  # the previous gradients of this slot have left
+        slot.grad.zero_()
+        p = slot.p
+        for v in range(self.n_views):
+            cm = slot.cam[v]
+            rs = GaussianRasterizationSettings(
+                image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=self.bg,
+                scale_modifier=1.0, viewmatrix=cm[0:16].view(4, 4), projmatrix=cm[16:32].view(4, 4),
+                sh_degree=self.sh_degree, campos=cm[32:35], prefiltered=False, debug=False)
+            _, _, st = _views.forward_view(rs, p["means3D"], p["opacities"], shs=p["shs"], scales=p["scales"],
+                                           rotations=p["rotations"])
+            _views.backward_view(st, slot.dL[v], slot.g)
+        if self.group is not False:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+                dist.all_reduce(slot.grad, group=self.group)
+        slot.ev_compute.record(cur)
+
+    def _copy_out(self, slot, host_grad):
+        with torch.cuda.stream(self.s_out):
+            self.s_out.wait_event(slot.ev_compute)
+            host_grad.copy_(slot.grad, non_blocking=True)
+            slot.ev_out.record(self.s_out)
+        slot.pending_out = host_grad
+        slot.used = True
+
+    # -- public ---------------------------------------------------------------------------------------------
+    def submit(self, host_param, host_cam, host_dL, host_grad):
+        """Queue one step.  All four tensors are pinned host tensors (flat params, (n_views,36) cameras,
+        (n_views,3,H,W) dL/dimage, flat gradient output).  The inputs must stay unchanged, and host_grad is not
+        valid, until a later submit()/flush() returns it.  Returns the list of host_grad tensors that became
+        valid during this call (steps complete in submission order)."""
+        for t, n in ((host_param, "host_param"), (host_cam, "host_cam"), (host_dL, "host_dL"), (host_grad, "host_grad")):
+            if t.is_cuda or not t.is_pinned():
+                raise RuntimeError(f"{n} must be a pinned host tensor")
+        if host_param.numel() != self.n_param or host_grad.numel() != self.n_param:
+            raise RuntimeError(f"host_param / host_grad need {self.n_param} elements")
+        done = []
+        slot = self.slots[self.n_submitted % len(self.slots)]
+        if self.staged is not None and slot is self.staged[0]:  # depth 1: nothing to overlap with
+            done += self.flush()
+        self._copy_in(slot, host_param, host_cam, host_dL)  # stream-ordered after the slot's previous compute
+        prev, self.staged = self.staged, (slot, host_grad)
+        self.n_submitted += 1
+        if prev is not None:
+            self._compute(prev[0])
+            self._copy_out(prev[0], prev[1])
+        # collect what has certainly had time to finish: every step older than the one just issued
+        for sl in self.slots:
+            if sl.pending_out is not None and (prev is None or sl is not prev[0]):
+                sl.ev_out.synchronize()
+                done.append(sl.pending_out)
+                sl.pending_out = None
+        return done
+
+    def flush(self):
+        """Run everything queued to completion; returns the host_grad tensors that became valid, in order."""
+        if self.staged is not None:
+            slot, host_grad = self.staged
+            self.staged = None
+            self._compute(slot)
+            self._copy_out(slot, host_grad)
+        done = []
+        n, d = self.n_submitted, len(self.slots)
+        for k in range(max(0, n - d), n):  # oldest first
+            slot = self.slots[k % d]
+            if slot.pending_out is not None:
+                slot.ev_out.synchronize()
+                done.append(slot.pending_out)
+                slot.pending_out = None
+        return done

@@ -77,7 +77,9 @@ size_t gsr_scratch_bytes(int32_t P, int64_t L_cap, int32_t W, int32_t H);  /* re
 /* ---- forward, phase 1: preprocess + fused prefix sum (forward.cu:155-256 preprocessCUDA,
  *      rasterizer_impl.cu:277 InclusiveSum).  Writes radii (P) and the geometry buffer, and the
  *      number of (tile, Gaussian) duplicates L to *num_rendered_dev (device u32); when
- *      num_rendered_host (pinned) is non-NULL it is also copied there asynchronously. ---- */
+ *      num_rendered_host is non-NULL it is also stored there by a kernel in stream order, so it must be
+ *      page-locked, device-mapped host memory (cudaHostAlloc / torch pin_memory under UVA); the store
+ *      does not use a copy engine and therefore never queues behind another stream's bulk transfer. ---- */
 int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void* scratch, size_t scratch_bytes,
                          uint32_t* num_rendered_dev, uint32_t* num_rendered_host, void* stream);
 
@@ -100,6 +102,17 @@ int gsr_backward(const gsr_inputs* in, const void* geom, const int32_t* radii, i
                  float* dL_dmean2D /*(P,3)*/, float* dL_dopacity /*(P,1)*/, float* dL_dcolor /*(P,3)*/,
                  float* dL_dmean3D /*(P,3)*/, float* dL_dcov3D /*(P,6)*/, float* dL_dsh /*(P,M,3)*/,
                  float* dL_dscale /*(P,3)*/, float* dL_drot /*(P,4)*/, float* dL_dobj /*(P,K)*/, void* stream);
+
+/* ---- backward of one view ADDED to the caller's gradient buffers (new; replaces the reference's pattern of
+ *      nine zero-filled tensors per view, rasterize_points.cu:151-159, followed by autograd's AccumulateGrad
+ *      add per attribute when a step sums several cameras, attack.py:481-494).  Rows of Gaussians the view did
+ *      not render are not touched; rendered rows are read-modify-written.  dL_dmean2D may be NULL.  The
+ *      buffers must have been initialised by the caller (zeroed at the start of a step).  K must be 0. ---- */
+int gsr_backward_accumulate(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
+                            const uint32_t* point_list, const void* image, void* scratch, size_t scratch_bytes,
+                            const float* dL_dpix, float* dL_dmean2D /*(P,3) or NULL*/, float* dL_dopacity,
+                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
+                            float* dL_drot, void* stream);
 
 /* ---- markVisible (rasterizer_impl.cu:141-153, checkFrustum :54-66); present is (P) bytes ---- */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

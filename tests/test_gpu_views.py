@@ -1,0 +1,124 @@
+"""GPU tests of the view-level accumulate API (views.forward_view / backward_view -> gsr_backward_accumulate)
+against the drop-in autograd path on the same inputs."""
+import numpy as np
+import pytest
+import torch
+
+import helpers as h
+
+pytestmark = pytest.mark.gpu
+
+
+def _autograd_sum(s, cams, dLs, **over):
+    import diff_gaussian_rasterization as dgr
+    t = h.scene_tensors(s)
+    m2s, imgs = [], []
+    for c, dL in zip(cams, dLs):
+        sc = dict(s); sc["cam"] = c
+        rs = h.settings_for(sc, **over)
+        m2 = torch.zeros((s["P"], 3), device="cuda", requires_grad=True)
+        img, radii = dgr.GaussianRasterizer(rs)(means3D=t["means3D"], means2D=m2, opacities=t["opacities"],
+                                                shs=t["shs"], scales=t["scales"], rotations=t["rotations"])
+        (img * dL).sum().backward()
+        m2s.append(m2.grad)
+        imgs.append(img.detach())
+    g = {k: v.grad for k, v in t.items()}
+    g["means2D"] = sum(m2s)
+    return imgs, g
+
+
+def test_accumulate_matches_sum_of_autograd_views():
+    from diff_gaussian_rasterization import views
+    from gsr_synth import ring_cameras
+    s = h.make_scene("tiny")
+    cams = ring_cameras(3, width=160, height=120)
+    rng = np.random.default_rng(5)
+    dLs = [torch.from_numpy(rng.standard_normal((3, 120, 160)).astype(np.float32)).cuda() for _ in cams]
+    imgs, ref = _autograd_sum(s, cams, dLs)
+    t = h.scene_tensors(s, requires_grad=False)
+    grads = {k: torch.zeros_like(v) for k, v in t.items()}
+    grads["means2D"] = torch.zeros((s["P"], 3), device="cuda")
+    states = []
+    for c in cams:  # all forwards first, then the backwards (state must not alias)
+        sc = dict(s); sc["cam"] = c
+        img, radii, st = views.forward_view(h.settings_for(sc), t["means3D"], t["opacities"], shs=t["shs"],
+                                            scales=t["scales"], rotations=t["rotations"])
+        states.append((img, st))
+    for (img, st), ref_img, dL in zip(states, imgs, dLs):
+        assert torch.equal(img, ref_img)  # same kernels, same inputs: bit-identical image
+        views.backward_view(st, dL, grads)
+    for k in ref:
+        ok, worst = h.grad_close(grads[k].cpu().numpy(), ref[k].cpu().numpy())
+        assert ok, (k, worst)
+
+
+def test_accumulate_leaves_unrendered_rows_untouched_and_adds_to_existing_values():
+    from diff_gaussian_rasterization import views
+    from gsr_synth import look_at_camera
+    s = h.make_scene("tiny")
+    c = s["cam"]
+    s["cam"] = look_at_camera((0.0, 0.0, -0.3), width=c["image_width"], height=c["image_height"])  # inside the cloud
+    t = h.scene_tensors(s, requires_grad=False)
+    rs = h.settings_for(s)
+    img, radii, st = views.forward_view(rs, t["means3D"], t["opacities"], shs=t["shs"], scales=t["scales"],
+                                        rotations=t["rotations"])
+    dL = torch.from_numpy(s["dL_dpix"]).cuda()
+    zero = {k: torch.zeros_like(v) for k, v in t.items()}
+    views.backward_view(st, dL, zero)
+    base = {k: float(v.abs().max()) for k, v in zero.items()}  # a start value on the scale of the gradient
+    start = {k: torch.full_like(v, base[k]) for k, v in t.items()}
+    views.backward_view(st, dL, start)
+    hidden = (radii == 0)
+    assert hidden.any() and (~hidden).any()
+    for k in zero:
+        z, v = zero[k].reshape(s["P"], -1), start[k].reshape(s["P"], -1)
+        assert torch.all(v[hidden] == base[k]) and torch.all(z[hidden] == 0.0), k
+        ok, worst = h.grad_close((v - base[k]).cpu().numpy(), z.cpu().numpy(), rtol=1e-3, atol_frac=1e-3)
+        assert ok, (k, worst)
+
+
+def test_accumulate_precomputed_colour_and_covariance_and_low_sh_degree():
+    from diff_gaussian_rasterization import views
+    sc, kw, gold = h.golden_case("tiny_precomp")
+    t = h.scene_tensors(sc, requires_grad=False)
+    col = torch.from_numpy(kw["colors_precomp"]).cuda()
+    cov = torch.from_numpy(kw["cov3D_precomp"]).cuda()
+    rs = h.settings_for(sc, bg=kw.get("bg"))
+    img, radii, st = views.forward_view(rs, t["means3D"], t["opacities"], colors_precomp=col, cov3D_precomp=cov)
+    assert float((img.cpu() - torch.from_numpy(gold["color"])).abs().max()) <= 1e-5
+    grads = dict(means3D=torch.zeros_like(t["means3D"]), opacities=torch.zeros_like(t["opacities"]),
+                 colors_precomp=torch.zeros_like(col), cov3D_precomp=torch.zeros_like(cov))
+    views.backward_view(st, torch.from_numpy(sc["dL_dpix"]).cuda(), grads)
+    for mine, theirs in (("means3D", "means3D"), ("opacities", "opacity"), ("colors_precomp", "colors"),
+                         ("cov3D_precomp", "cov3D")):
+        a = grads[mine].cpu().numpy().reshape(-1)
+        ok, worst = h.grad_close(a, gold["grads"][theirs].reshape(-1)[: a.size])
+        assert ok, (mine, worst)
+    # SH degree 1 (only the first 4 coefficients receive gradient)
+    sc, kw, gold = h.golden_case("tiny_sh1_bg")
+    t = h.scene_tensors(sc, requires_grad=False)
+    img, radii, st = views.forward_view(h.settings_for(sc, bg=kw.get("bg")), t["means3D"], t["opacities"], shs=t["shs"],
+                                        scales=t["scales"], rotations=t["rotations"])
+    assert float((img.cpu() - torch.from_numpy(gold["color"])).abs().max()) <= 1e-5
+    grads = {k: torch.zeros_like(v) for k, v in t.items()}
+    views.backward_view(st, torch.from_numpy(sc["dL_dpix"]).cuda(), grads)
+    for mine, theirs in (("means3D", "means3D"), ("opacities", "opacity"), ("shs", "sh"), ("scales", "scales"),
+                         ("rotations", "rotations")):
+        a = grads[mine].cpu().numpy().reshape(-1)
+        ok, worst = h.grad_close(a, gold["grads"][theirs].reshape(-1)[: a.size])
+        assert ok, (mine, worst)
+
+
+def test_backward_view_argument_errors():
+    from diff_gaussian_rasterization import views
+    s = h.make_scene("tiny")
+    t = h.scene_tensors(s, requires_grad=False)
+    with pytest.raises(Exception):
+        views.forward_view(h.settings_for(s), t["means3D"], t["opacities"], scales=t["scales"], rotations=t["rotations"])
+    img, radii, st = views.forward_view(h.settings_for(s), t["means3D"], t["opacities"], shs=t["shs"],
+                                        scales=t["scales"], rotations=t["rotations"])
+    dL = torch.from_numpy(s["dL_dpix"]).cuda()
+    with pytest.raises(Exception):  # missing shs buffer
+        views.backward_view(st, dL, dict(means3D=torch.zeros_like(t["means3D"]), opacities=torch.zeros_like(t["opacities"])))
+    with pytest.raises(Exception):
+        views.backward_view(st, dL, dict(bogus=torch.zeros(1, device="cuda")))
