@@ -131,9 +131,9 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   GSR_TRY(debug_sync(in, st, "preprocess"));
   // order the Gaussians by (depth bits, index): 4 passes, the result lands back in (dkeys_a, geom.perm)
   { StageScope ps(ST_SORT, st);
-    GSR_TRY(launch_sort_pairs_pingpong_u32(s.dkeys_a, g.perm, s.dkeys_b, s.dvals_b, in->P, 32, s.sort_temp, nullptr, st)); }
+    GSR_TRY(launch_sort_pairs_pingpong_u32(s.dkeys_a, g.perm, s.dkeys_b, s.dvals_b, in->P, 32, s.sort_temp, nullptr, false, st)); }
   GSR_TRY(debug_sync(in, st, "depth_sort"));
-  { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, st)); }
+  { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, num_rendered_dev, st)); }
   GSR_TRY(debug_sync(in, st, "sorted_scan"));
   if (num_rendered_host) {
     publish_count_kernel<<<1, 1, 0, st>>>(num_rendered_dev, num_rendered_host);
@@ -177,9 +177,15 @@ int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* ra
   uint32_t* v0 = (passes & 1) ? s.vals_a : point_list;
   uint32_t* v1 = (passes & 1) ? point_list : s.vals_a;
   if (L > 0) {
-    { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_duplicate_tiles(in->P, g, gx, k0, v0, st)); }
+    // the tile-id sort has <= 2 passes for up to 65536 tiles: duplicate_tiles builds its digit histograms
+    const bool fused_hist = end_bit <= 16;
+    uint32_t* hist = nullptr;
+    { StageScope ps(ST_DUPLICATE, st);
+      if (fused_hist) GSR_TRY(sort_prepare(s.sort_temp, L, passes, &hist, st));
+      GSR_TRY(launch_duplicate_tiles(in->P, g, gx, k0, v0, hist, end_bit, st)); }
     GSR_TRY(debug_sync(in, st, "duplicate_tiles"));
-    { StageScope ps(ST_SORT, st); GSR_TRY(launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, L, end_bit, s.sort_temp, nullptr, st)); }
+    { StageScope ps(ST_SORT, st);
+      GSR_TRY(launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, L, end_bit, s.sort_temp, nullptr, fused_hist, st)); }
     GSR_TRY(debug_sync(in, st, "sort"));
   }
   { StageScope ps(ST_RANGES, st); GSR_TRY(launch_tile_ranges(L, s.tkeys_a, im.ranges, gx * gy, st)); }
@@ -276,11 +282,20 @@ int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64
 #define F(nm, ptr, cnt) if (!strcmp(name, nm)) { src = ptr; bytes = (cnt); }
   F("depths", g.depths, n * 4) F("means2D", g.means2D, n * 8) F("cov3D", g.cov3D, n * 24)
   F("conic_opacity", g.conic_opacity, n * 16) F("rgb", g.rgb_thr, n * 16) F("clamped", g.clamped, n)
-  F("tiles_touched", g.tiles_touched, n * 4) F("point_offsets", g.point_offsets, n * 4) F("rects", g.rects, n * 8)
+  F("tiles_touched", g.tiles_touched, n * 4) F("rects", g.rects, n * 8)
   F("perm", g.perm, n * 4) F("offsets_sorted", g.offsets_sorted, n * 4)
   F("final_T", im.final_T, HW * 4) F("n_contrib", im.n_contrib, HW * 4) F("ranges", im.ranges, (size_t)gx * gy * 8)
   F("tiles_sorted", s.tkeys_a, (size_t)L * 4)
 #undef F
+  if (!strcmp(name, "point_offsets")) {
+    // the reference's InclusiveSum over tiles_touched in index order (rasterizer_impl.cu:277), computed on demand
+    bytes = n * 4;
+    if (dst) {
+      if (!scratch || cap < (int64_t)bytes) { set_error("debug_fetch: point_offsets needs scratch and cap >= 4 P"); return GSR_ERR_INVALID; }
+      GSR_TRY(launch_index_scan(P, g, s, (uint32_t*)dst, (cudaStream_t)stream));
+    }
+    return (int64_t)bytes;
+  }
   if (!strcmp(name, "keys_sorted")) {
     // the reference's sorted 64-bit keys (tile << 32 | depth bits), rebuilt from the sorted tile ids + point list
     bytes = (size_t)L * 8;

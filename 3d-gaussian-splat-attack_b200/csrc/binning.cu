@@ -18,23 +18,31 @@ __device__ __forceinline__ unsigned long long pack_status(uint32_t flag, uint32_
   return ((unsigned long long)flag << 32) | v;
 }
 
-// offsets_sorted[i] = sum_{k<=i} tiles_touched[perm[k]]; single pass, decoupled look-back over 1024-item blocks
+// offsets[i] = sum_{k<=i} tiles_touched[perm ? perm[k] : k]; single pass over 1024-item blocks, decoupled
+// look-back done by a whole warp (32 predecessors per round trip).  The last block also stores the grand
+// total (= num_rendered, rasterizer_impl.cu:281) when `total_out` is given.
 __global__ void __launch_bounds__(256)
-sorted_scan_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ tiles_touched,
-                   uint32_t* __restrict__ offsets_sorted, unsigned long long* status, uint32_t* ticket) {
+scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ tiles_touched,
+                  uint32_t* __restrict__ offsets, unsigned long long* status, uint32_t* ticket,
+                  uint32_t* __restrict__ total_out, int nblocks) {
   __shared__ uint32_t s_tile, s_warp[8], s_prefix;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  if (tid == 0) s_tile = atomicAdd(ticket, 1u);  // blocks are numbered in start order -> look-back cannot deadlock
   __syncthreads();
   const uint32_t tile = s_tile;
   const int base = (int)tile * SCAN_ITEMS + tid * 4;
   uint32_t v[4], sum = 0;
   if (base + 3 < P) {
-    const uint4 pi = *reinterpret_cast<const uint4*>(perm + base);
-    v[0] = tiles_touched[pi.x]; v[1] = tiles_touched[pi.y]; v[2] = tiles_touched[pi.z]; v[3] = tiles_touched[pi.w];
+    if (perm) {
+      const uint4 pi = *reinterpret_cast<const uint4*>(perm + base);
+      v[0] = tiles_touched[pi.x]; v[1] = tiles_touched[pi.y]; v[2] = tiles_touched[pi.z]; v[3] = tiles_touched[pi.w];
+    } else {
+      const uint4 t = *reinterpret_cast<const uint4*>(tiles_touched + base);
+      v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
   } else {
 #pragma unroll
-    for (int k = 0; k < 4; k++) v[k] = base + k < P ? tiles_touched[perm[base + k]] : 0u;
+    for (int k = 0; k < 4; k++) v[k] = base + k < P ? tiles_touched[perm ? perm[base + k] : (uint32_t)(base + k)] : 0u;
   }
 #pragma unroll
   for (int k = 0; k < 4; k++) { sum += v[k]; v[k] = sum; }
@@ -54,79 +62,104 @@ sorted_scan_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __r
       if (lane >= o) w += t;
     }
     if (lane < 8) s_warp[lane] = w;
-  }
-  __syncthreads();
-  const uint32_t block_total = s_warp[7];
-  if (tid == 0) {
+    const uint32_t block_total = __shfl_sync(0xffffffffu, w, 7);
     volatile unsigned long long* st = status;
     uint32_t excl = 0;
     if (tile == 0) {
-      st[0] = pack_status(2, block_total);
+      if (lane == 0) st[0] = pack_status(2, block_total);
     } else {
-      st[tile] = pack_status(1, block_total);
-      __threadfence();
-      int64_t j = (int64_t)tile - 1;
+      if (lane == 0) st[tile] = pack_status(1, block_total);
+      int64_t j = (int64_t)tile - 1 - lane;  // lane 0 looks at the nearest predecessor
       while (true) {
-        const unsigned long long w = st[j];
-        const uint32_t flag = (uint32_t)(w >> 32);
-        if (flag == 0) continue;
-        excl += (uint32_t)w;
-        if (flag == 2) break;
-        j--;
+        const unsigned long long w2 = j >= 0 ? st[j] : pack_status(2, 0);  // before block 0: prefix 0
+        const uint32_t flag = (uint32_t)(w2 >> 32);
+        const uint32_t ready = __ballot_sync(0xffffffffu, flag != 0);
+        const uint32_t pref = __ballot_sync(0xffffffffu, flag == 2);
+        const uint32_t need = pref ? ((2u << (__ffs(pref) - 1)) - 1u) : 0xffffffffu;  // lanes up to the first prefix
+        if ((ready & need) != need) continue;  // a needed predecessor has not published yet: look again
+        uint32_t part = (need >> lane) & 1u ? (uint32_t)w2 : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        excl += part;
+        if (pref) break;
+        j -= 32;
       }
-      st[tile] = pack_status(2, excl + block_total);
+      if (lane == 0) st[tile] = pack_status(2, excl + block_total);
     }
-    s_prefix = excl;
+    if (lane == 0) {
+      s_prefix = excl;
+      if (total_out && (int)tile == nblocks - 1) *total_out = excl + block_total;
+    }
   }
   __syncthreads();
   const uint32_t off = s_prefix + (warp ? s_warp[warp - 1] : 0u) + (incl - sum);
   if (base + 3 < P) {
-    *reinterpret_cast<uint4*>(offsets_sorted + base) = make_uint4(off + v[0], off + v[1], off + v[2], off + v[3]);
+    *reinterpret_cast<uint4*>(offsets + base) = make_uint4(off + v[0], off + v[1], off + v[2], off + v[3]);
   } else {
 #pragma unroll
-    for (int k = 0; k < 4; k++) if (base + k < P) offsets_sorted[base + k] = off + v[k];
+    for (int k = 0; k < 4; k++) if (base + k < P) offsets[base + k] = off + v[k];
   }
 }
 
-// One lane per Gaussian (in depth order) for small rects; rects larger than DUP_SOLO_MAX are expanded by the
-// whole warp (coalesced 32-wide stores), which removes the reference's load imbalance on large splats.
-// Tiles of one Gaussian are emitted in row-major order, as the reference does.
+// Emits the (tile id, Gaussian) pairs in depth order.  One lane per Gaussian for small rects; rects larger than
+// DUP_SOLO_MAX are expanded by the whole warp (coalesced 32-wide stores), which removes the reference's load
+// imbalance on large splats.  Tiles of one Gaussian are emitted in row-major order, as the reference does.
+// Blocks stride over 256-Gaussian chunks and also build the digit histograms of the tile-id sort that follows
+// (hist[p * 256 + digit of pass p]), so that sort needs no histogram pass of its own.
 __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets_sorted,
                        const uint32_t* __restrict__ tiles_touched, const ushort4* __restrict__ rects, int gx,
-                       uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-  const int i = blockIdx.x * DUP_THREADS + threadIdx.x;
+                       uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ hist,
+                       uint32_t mask1) {
+  __shared__ uint32_t sh[2 * 256];
+  for (int k = threadIdx.x; k < 2 * 256; k += DUP_THREADS) sh[k] = 0;
+  __syncthreads();
   const int lane = threadIdx.x & 31;
-  uint32_t area = 0, off = 0, x0 = 0, y0 = 0, w = 0, id = 0;
-  if (i < P) {
-    id = perm[i];
-    area = tiles_touched[id];
-    if (area > 0) {
-      const ushort4 r = rects[id];
-      x0 = r.x; y0 = r.y; w = (uint32_t)r.z - r.x;
-      off = i == 0 ? 0u : offsets_sorted[i - 1];
+  const int nchunks = (P + DUP_THREADS - 1) / DUP_THREADS;
+  for (int chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+    const int i = chunk * DUP_THREADS + threadIdx.x;
+    uint32_t area = 0, off = 0, x0 = 0, y0 = 0, w = 0, id = 0;
+    if (i < P) {
+      id = perm[i];
+      area = tiles_touched[id];
+      if (area > 0) {
+        const ushort4 r = rects[id];
+        x0 = r.x; y0 = r.y; w = (uint32_t)r.z - r.x;
+        off = i == 0 ? 0u : offsets_sorted[i - 1];
+      }
+    }
+    if (area > 0 && area <= DUP_SOLO_MAX) {
+      uint32_t x = 0, y = 0;
+      for (uint32_t t = 0; t < area; t++) {
+        const uint32_t key = (y0 + y) * gx + x0 + x;
+        keys[off + t] = key;
+        vals[off + t] = id;
+        atomicAdd(&sh[key & 255u], 1u);
+        atomicAdd(&sh[256 + ((key >> 8) & mask1)], 1u);
+        if (++x == w) { x = 0; y++; }
+      }
+    }
+    uint32_t big = __ballot_sync(0xffffffffu, area > DUP_SOLO_MAX);
+    while (big) {
+      const int src = __ffs(big) - 1;
+      big &= big - 1;
+      const uint32_t a = __shfl_sync(0xffffffffu, area, src), o = __shfl_sync(0xffffffffu, off, src);
+      const uint32_t bx = __shfl_sync(0xffffffffu, x0, src), by = __shfl_sync(0xffffffffu, y0, src);
+      const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bid = __shfl_sync(0xffffffffu, id, src);
+      for (uint32_t t = lane; t < a; t += 32) {
+        const uint32_t y = t / bw, x = t - y * bw;
+        const uint32_t key = (by + y) * gx + bx + x;
+        keys[o + t] = key;
+        vals[o + t] = bid;
+        atomicAdd(&sh[key & 255u], 1u);
+        atomicAdd(&sh[256 + ((key >> 8) & mask1)], 1u);
+      }
     }
   }
-  if (area > 0 && area <= DUP_SOLO_MAX) {
-    uint32_t x = 0, y = 0;
-    for (uint32_t t = 0; t < area; t++) {
-      keys[off + t] = (y0 + y) * gx + x0 + x;
-      vals[off + t] = id;
-      if (++x == w) { x = 0; y++; }
-    }
-  }
-  uint32_t big = __ballot_sync(0xffffffffu, area > DUP_SOLO_MAX);
-  while (big) {
-    const int src = __ffs(big) - 1;
-    big &= big - 1;
-    const uint32_t a = __shfl_sync(0xffffffffu, area, src), o = __shfl_sync(0xffffffffu, off, src);
-    const uint32_t bx = __shfl_sync(0xffffffffu, x0, src), by = __shfl_sync(0xffffffffu, y0, src);
-    const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bid = __shfl_sync(0xffffffffu, id, src);
-    for (uint32_t t = lane; t < a; t += 32) {
-      const uint32_t y = t / bw, x = t - y * bw;
-      keys[o + t] = (by + y) * gx + bx + x;
-      vals[o + t] = bid;
-    }
+  __syncthreads();
+  if (hist) {
+    for (int k = threadIdx.x; k < 2 * 256; k += DUP_THREADS)
+      if (sh[k]) atomicAdd(&hist[k], sh[k]);
   }
 }
 
@@ -157,16 +190,32 @@ __global__ void rebuild_keys_kernel(int64_t L, const uint32_t* __restrict__ tile
 
 }  // namespace
 
-int launch_sorted_scan(int P, const Geom& g, Scratch& s, cudaStream_t st) {
-  sorted_scan_kernel<<<(P + SCAN_ITEMS - 1) / SCAN_ITEMS, 256, 0, st>>>(P, g.perm, g.tiles_touched, g.offsets_sorted,
-                                                                        s.scan2_status, s.scan_ticket + 1);
-  GSR_LAUNCH_CHECK("sorted_scan_kernel");
+int launch_sorted_scan(int P, const Geom& g, Scratch& s, uint32_t* num_rendered_dev, cudaStream_t st) {
+  const int nb = (P + SCAN_ITEMS - 1) / SCAN_ITEMS;
+  scan_tiles_kernel<<<nb, 256, 0, st>>>(P, g.perm, g.tiles_touched, g.offsets_sorted, s.scan2_status, s.scan_ticket + 1,
+                                        num_rendered_dev, nb);
+  GSR_LAUNCH_CHECK("scan_tiles_kernel");
   return GSR_OK;
 }
 
-int launch_duplicate_tiles(int P, const Geom& g, int gx, uint32_t* tile_keys, uint32_t* vals, cudaStream_t st) {
-  duplicate_tiles_kernel<<<(P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, st>>>(
-      P, g.perm, g.offsets_sorted, g.tiles_touched, g.rects, gx, tile_keys, vals);
+// The reference's point_offsets (InclusiveSum in index order, rasterizer_impl.cu:277); parity tests only.
+int launch_index_scan(int P, const Geom& g, Scratch& s, uint32_t* out, cudaStream_t st) {
+  const int nb = (P + SCAN_ITEMS - 1) / SCAN_ITEMS;
+  GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_status, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
+  GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_ticket, 0, sizeof(uint32_t), st));
+  scan_tiles_kernel<<<nb, 256, 0, st>>>(P, nullptr, g.tiles_touched, out, s.scan_status, s.scan_ticket, nullptr, nb);
+  GSR_LAUNCH_CHECK("scan_tiles_kernel");
+  return GSR_OK;
+}
+
+// end_bit <= 16: the tile-id sort has at most two 8-bit passes, whose histograms are built here
+int launch_duplicate_tiles(int P, const Geom& g, int gx, uint32_t* tile_keys, uint32_t* vals, uint32_t* hist,
+                           int end_bit, cudaStream_t st) {
+  const int nchunks = (P + DUP_THREADS - 1) / DUP_THREADS;
+  const int blocks = nchunks < 148 * 6 ? nchunks : 148 * 6;
+  const uint32_t mask1 = end_bit > 8 ? (1u << (end_bit - 8)) - 1u : 0u;
+  duplicate_tiles_kernel<<<blocks, DUP_THREADS, 0, st>>>(P, g.perm, g.offsets_sorted, g.tiles_touched, g.rects, gx,
+                                                         tile_keys, vals, hist, mask1);
   GSR_LAUNCH_CHECK("duplicate_tiles_kernel");
   return GSR_OK;
 }

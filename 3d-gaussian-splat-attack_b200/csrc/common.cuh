@@ -59,7 +59,6 @@ struct Geom {
   float* cov3D;            // [6P]
   uint8_t* clamped;        // [P]  bit c set <=> channel c was clamped at 0 (forward.cu:66-69)
   uint32_t* tiles_touched; // [P]
-  uint32_t* point_offsets; // [P]  inclusive prefix sum of tiles_touched
   ushort4* rects;          // [P]  (x0, y0, x1, y1) tile rect (auxiliary.h:46-56)
   uint32_t* perm;          // [P]  Gaussian indices in (depth bits, index) order
   uint32_t* offsets_sorted;// [P]  inclusive prefix sum of tiles_touched[perm[.]]
@@ -74,7 +73,6 @@ struct Geom {
     cov3D = c.take<float>(6 * n);
     clamped = c.take<uint8_t>(n);
     tiles_touched = c.take<uint32_t>(n);
-    point_offsets = c.take<uint32_t>(n);
     rects = c.take<ushort4>(n);
     perm = c.take<uint32_t>(n);
     offsets_sorted = c.take<uint32_t>(n);
@@ -110,16 +108,19 @@ struct SortTemp {
   uint32_t* hist;     // [SORT_MAX_PASSES][256] digit histograms -> exclusive offsets
   uint32_t* tickets;  // [SORT_MAX_PASSES] dynamic tile ids
   uint32_t* status;   // [SORT_MAX_PASSES][tiles][256] decoupled look-back words
-  size_t zero_bytes;  // prefix of the buffer that must be zeroed before a sort
+  size_t status_off, pass_stride;
   size_t bytes;
   SortTemp(void* buf, int64_t n) {
     Carver c(buf);
     hist = c.take<uint32_t>(SORT_MAX_PASSES * 256);
     tickets = c.take<uint32_t>(64);
+    status_off = c.off;
+    pass_stride = (size_t)sort_tiles(n) * 256 * sizeof(uint32_t);
     status = c.take<uint32_t>((size_t)SORT_MAX_PASSES * sort_tiles(n) * 256);
-    zero_bytes = c.off;
     bytes = c.off;
   }
+  // prefix of the buffer that must be zeroed before a sort of `passes` passes
+  size_t zero_bytes(int passes) const { return status_off + (size_t)passes * pass_stride; }
 };
 
 // Reusable scratch (not needed after the call that used it returns).
@@ -131,7 +132,7 @@ struct SortTemp {
 constexpr int PRE_THREADS = 256;  // Gaussians per preprocess block
 constexpr int SCAN_ITEMS = 1024;  // Gaussians per block of the sorted-order scan
 struct Scratch {
-  unsigned long long* scan_status;   // [pre_blocks] look-back words of the fused prefix sum
+  unsigned long long* scan_status;   // [pre_blocks] look-back words of the index-order prefix sum (debug fetch only)
   unsigned long long* scan2_status;  // [scan_blocks] look-back words of the sorted-order prefix sum
   uint32_t* scan_ticket;             // [64] ([0] preprocess, [1] sorted-order scan)
   uint32_t* flags;                   // [64] flags[0] = prefiltered violation
@@ -169,14 +170,17 @@ struct Scratch {
 // ---- stage launchers (each returns a gsr_status) ---------------------------------------------
 int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch& s, uint32_t* num_rendered_dev,
                           cudaStream_t st);
-int launch_sorted_scan(int P, const Geom& g, Scratch& s, cudaStream_t st);
-int launch_duplicate_tiles(int P, const Geom& g, int gx, uint32_t* tile_keys, uint32_t* vals, cudaStream_t st);
+int launch_sorted_scan(int P, const Geom& g, Scratch& s, uint32_t* num_rendered_dev, cudaStream_t st);
+int launch_index_scan(int P, const Geom& g, Scratch& s, uint32_t* out, cudaStream_t st);
+int launch_duplicate_tiles(int P, const Geom& g, int gx, uint32_t* tile_keys, uint32_t* vals, uint32_t* hist,
+                           int end_bit, cudaStream_t st);
+int sort_prepare(void* temp, int64_t n, int passes, uint32_t** hist_out, cudaStream_t st);
 int launch_rebuild_keys(int64_t L, const uint32_t* tile_keys, const uint32_t* point_list, const float* depths,
                         uint64_t* keys_out, cudaStream_t st);
 int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
                                int end_bit, void* temp, int* passes_out, cudaStream_t st);
 int launch_sort_pairs_pingpong_u32(uint32_t* keys0, uint32_t* vals0, uint32_t* keys1, uint32_t* vals1, int64_t n,
-                                   int end_bit, void* temp, int* passes_out, cudaStream_t st);
+                                   int end_bit, void* temp, int* passes_out, bool hist_ready, cudaStream_t st);
 int launch_tile_ranges(int64_t L, const uint32_t* tile_keys_sorted, uint2* ranges, int tiles, cudaStream_t st);
 int launch_blend_fwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
                      float* out_color, float* out_objects, cudaStream_t st);

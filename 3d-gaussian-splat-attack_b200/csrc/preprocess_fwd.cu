@@ -1,9 +1,11 @@
-// preprocess_fwd.cu -- per-Gaussian forward preprocess fused with the prefix sum of tiles_touched.
+// preprocess_fwd.cu -- per-Gaussian forward preprocess.
 //
 // Replaces preprocessCUDA (DGR/cuda_rasterizer/forward.cu:155-256: in_frustum auxiliary.h:139-164,
 // computeCov3D forward.cu:118-152, computeCov2D :74-113, ndc2Pix auxiliary.h:41-44, getRect :46-56,
-// computeColorFromSH forward.cu:20-71), cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:277) and
-// checkFrustum (rasterizer_impl.cu:54-66).
+// computeColorFromSH forward.cu:20-71) and checkFrustum (rasterizer_impl.cu:54-66).  The reference's
+// cub::DeviceScan::InclusiveSum over tiles_touched in index order (rasterizer_impl.cu:277) is not needed by
+// this design's binning (binning.cu scans in depth order, which also yields num_rendered); index_scan in
+// binning.cu reproduces it on demand for the parity tests.
 //
 // Bit-exactness: depths, radii, pixel centres, conics and RGB feed the sort keys, the tile lists and
 // the alpha thresholds.  Which mul/add pairs end up fused is decided twice in the reference build:
@@ -168,24 +170,15 @@ __device__ __forceinline__ void sh_to_rgb(int deg, float px, float py, float pz,
   }
 }
 
-// look-back status word: (flag << 32) | value ; flag 1 = block aggregate, 2 = inclusive prefix
-__device__ __forceinline__ unsigned long long pack_status(uint32_t flag, uint32_t v) {
-  return ((unsigned long long)flag << 32) | v;
-}
-
 __global__ void __launch_bounds__(PRE_THREADS)
-preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, unsigned long long* scan_status,
-                      uint32_t* scan_ticket, uint32_t* flags, uint32_t* num_rendered, uint32_t* __restrict__ dkeys,
-                      int nblocks) {
+preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32_t* flags,
+                      uint32_t* __restrict__ dkeys) {
   __shared__ Cam cam;
-  __shared__ uint32_t s_tile, s_warp_sums[PRE_THREADS / 32], s_prefix;
   const int tid = threadIdx.x;
-  if (tid == 0) s_tile = atomicAdd(scan_ticket, 1u);  // tiles are claimed in launch order -> look-back cannot deadlock
   if (tid < 16) { cam.view[tid] = in.viewmatrix[tid]; cam.proj[tid] = in.projmatrix[tid]; }
   if (tid < 3) cam.campos[tid] = in.campos[tid];
   __syncthreads();
-  const uint32_t tile = s_tile;
-  const int idx = (int)(tile * PRE_THREADS + tid);
+  const int idx = (int)(blockIdx.x * PRE_THREADS + tid);
   const int W = in.W, H = in.H;
   const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
 
@@ -277,51 +270,6 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, unsign
     g.perm[idx] = (uint32_t)idx;
   }
 
-  // ---- fused inclusive prefix sum over tiles_touched (decoupled look-back across blocks) ----
-  const int lane = tid & 31, warp = tid >> 5;
-  uint32_t incl = touched;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += v;
-  }
-  if (lane == 31) s_warp_sums[warp] = incl;
-  __syncthreads();
-  if (warp == 0) {
-    uint32_t w = lane < PRE_THREADS / 32 ? s_warp_sums[lane] : 0;
-#pragma unroll
-    for (int o = 1; o < PRE_THREADS / 32; o <<= 1) {
-      uint32_t v = __shfl_up_sync(0xffffffffu, w, o);
-      if (lane >= o) w += v;
-    }
-    if (lane < PRE_THREADS / 32) s_warp_sums[lane] = w;  // inclusive over warps
-  }
-  __syncthreads();
-  const uint32_t block_total = s_warp_sums[PRE_THREADS / 32 - 1];
-  if (tid == 0) {
-    volatile unsigned long long* st = scan_status;
-    uint32_t excl = 0;
-    if (tile == 0) {
-      st[0] = pack_status(2, block_total);
-    } else {
-      st[tile] = pack_status(1, block_total);
-      __threadfence();
-      int64_t j = (int64_t)tile - 1;
-      while (true) {
-        unsigned long long w = st[j];
-        const uint32_t flag = (uint32_t)(w >> 32);
-        if (flag == 0) continue;
-        excl += (uint32_t)w;
-        if (flag == 2) break;
-        j--;
-      }
-      st[tile] = pack_status(2, excl + block_total);
-    }
-    s_prefix = excl;
-    if ((int)tile == nblocks - 1) *num_rendered = excl + block_total;
-  }
-  __syncthreads();
-  if (idx < in.P) g.point_offsets[idx] = s_prefix + (warp ? s_warp_sums[warp - 1] : 0u) + incl;
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
@@ -338,8 +286,8 @@ int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch
                           cudaStream_t st) {
   const int nblocks = (in.P + PRE_THREADS - 1) / PRE_THREADS;
   GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_status, 0, s.scan_zero_bytes, st));
-  preprocess_fwd_kernel<<<nblocks, PRE_THREADS, 0, st>>>(in, g, radii, s.scan_status, s.scan_ticket, s.flags,
-                                                          num_rendered_dev, s.dkeys_a, nblocks);
+  (void)num_rendered_dev;  // written by the depth-order scan (launch_sorted_scan)
+  preprocess_fwd_kernel<<<nblocks, PRE_THREADS, 0, st>>>(in, g, radii, s.flags, s.dkeys_a);
   GSR_LAUNCH_CHECK("preprocess_fwd_kernel");
   return GSR_OK;
 }

@@ -142,14 +142,24 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
   S.digit_off[tid] = doff;
   uint32_t excl = 0;
   if (tile != 0) {
-    __threadfence();
+    // decoupled look-back, four predecessors per round trip (independent loads); a status word carries both
+    // flag and value, so no fence is needed around it
     int64_t j = (int64_t)tile - 1;
     while (true) {
-      const uint32_t w = st[(size_t)j * 256 + tid];
-      if ((w & (ST_AGG | ST_PREFIX)) == 0) continue;
-      excl += w & ST_MASK;
-      if (w & ST_PREFIX) break;
-      j--;
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) { w[k] = 1u << 31; if (j - k >= 0) w[k] = st[(size_t)(j - k) * 256 + tid]; }
+      bool done = false, stop = false;
+      int adv = 0;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        if (!done && !stop) {
+          if ((w[k] & (ST_AGG | ST_PREFIX)) == 0) stop = true;
+          else { excl += w[k] & ST_MASK; adv = k + 1; done = (w[k] & ST_PREFIX) != 0; }
+        }
+      }
+      if (done) break;
+      j -= adv;
     }
     st[(size_t)tile * 256 + tid] = ST_PREFIX | ((excl + count) & ST_MASK);
   }
@@ -183,7 +193,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 // result is in pair (passes & 1).  Returns the pass count through *passes_out.
 template <typename KeyT>
 static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32_t* vals1, int64_t n, int end_bit,
-                               void* temp, int* passes_out, cudaStream_t st) {
+                               void* temp, int* passes_out, bool hist_ready, cudaStream_t st) {
   const int passes = (end_bit + 7) / 8;
   if (passes_out) *passes_out = passes;
   if (passes < 1 || passes > (int)sizeof(KeyT) || passes > SORT_MAX_PASSES) {
@@ -192,10 +202,12 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
   if (n >= (int64_t)ST_MASK) { set_error("sort: %lld pairs exceed the 2^30 limit", (long long)n); return GSR_ERR_INVALID; }
   if (n == 0) return GSR_OK;
   SortTemp T(temp, n);
-  GSR_CUDA_CHECK(cudaMemsetAsync(temp, 0, T.zero_bytes, st));
-  const int hist_blocks = (int)min((int64_t)148 * 8, (n + 2047) / 2048);
-  sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys0, n, passes, end_bit, T.hist);
-  GSR_LAUNCH_CHECK("sort_histogram_kernel");
+  if (!hist_ready) {  // otherwise the caller zeroed `temp` and the producer of keys0 filled T.hist (sort_prepare)
+    GSR_CUDA_CHECK(cudaMemsetAsync(temp, 0, T.zero_bytes(passes), st));
+    const int hist_blocks = (int)min((int64_t)148 * 8, (n + 2047) / 2048);
+    sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys0, n, passes, end_bit, T.hist);
+    GSR_LAUNCH_CHECK("sort_histogram_kernel");
+  }
   sort_scan_hist_kernel<<<1, 32 * SORT_MAX_PASSES, 0, st>>>(T.hist, passes);
   GSR_LAUNCH_CHECK("sort_scan_hist_kernel");
   GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -217,11 +229,20 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
 
 int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
                                int end_bit, void* temp, int* passes_out, cudaStream_t st) {
-  return sort_pairs_pingpong<uint64_t>(keys0, vals0, keys1, vals1, n, end_bit, temp, passes_out, st);
+  return sort_pairs_pingpong<uint64_t>(keys0, vals0, keys1, vals1, n, end_bit, temp, passes_out, false, st);
 }
 int launch_sort_pairs_pingpong_u32(uint32_t* keys0, uint32_t* vals0, uint32_t* keys1, uint32_t* vals1, int64_t n,
-                                   int end_bit, void* temp, int* passes_out, cudaStream_t st) {
-  return sort_pairs_pingpong<uint32_t>(keys0, vals0, keys1, vals1, n, end_bit, temp, passes_out, st);
+                                   int end_bit, void* temp, int* passes_out, bool hist_ready, cudaStream_t st) {
+  return sort_pairs_pingpong<uint32_t>(keys0, vals0, keys1, vals1, n, end_bit, temp, passes_out, hist_ready, st);
+}
+
+// Zeroes the sort's temp block and returns where the producer of the keys must accumulate the digit
+// histograms (pass p, digit d -> hist[p * 256 + d]) when it wants to skip the sort's own histogram pass.
+int sort_prepare(void* temp, int64_t n, int passes, uint32_t** hist_out, cudaStream_t st) {
+  SortTemp T(temp, n);
+  GSR_CUDA_CHECK(cudaMemsetAsync(temp, 0, T.zero_bytes(passes), st));
+  *hist_out = T.hist;
+  return GSR_OK;
 }
 
 }  // namespace gsr
