@@ -15,19 +15,25 @@
 //     phase 2 (lane = entry x pixel-half) sweeps the panel, each lane accumulating the 9 sums of its
 //     own entry in registers, then one shuffle per value joins the two halves and one RED per value
 //     goes to the packed [P][12] accumulator (the reference issues 9 atomics per contributing pixel).
-// The contribution test uses exactly the forward arithmetic, so the set of contributing pairs is
-// the forward's.  Sum order differs from the reference's atomics -> gradients are compared with
-// a tolerance.  Bound: FP32 issue.
+//   * the reference's three per-channel running colours (accum_rec, backward.cu:499-521) collapse into one
+//     running scalar: dL/dalpha_j = T_j (c_j . dL/dpixel) - behind_j / (1 - alpha_j), where behind_j =
+//     sum_{k behind j} (c_k . dL/dpixel) alpha_k T_k + T_final (bg . dL/dpixel)  (same algebra, 11 instead of
+//     ~24 instructions per pair);
+//   * exp() is MUFU.EX2 of the scaled argument; the decision "did this pair contribute" is still the
+//     forward's, bit for bit (an alpha next to the 1/255 threshold is redone with the forward's expf).
+// Sum order and roundings differ from the reference's atomics -> gradients are compared with a tolerance
+// (measured on C2 against the reference CUDA: the same distance as two runs of the reference from each other,
+// tools/grad_ratio.py).  Bound: FP32 issue.
 #include "blend_common.cuh"
 
 namespace gsr {
 namespace {
 
 #ifndef GSR_BWD_GRP
-#define GSR_BWD_GRP 16
+#define GSR_BWD_GRP 8
 #endif
 #ifndef GSR_BWD_MINBLOCKS
-#define GSR_BWD_MINBLOCKS 4
+#define GSR_BWD_MINBLOCKS 5
 #endif
 constexpr int GRP = GSR_BWD_GRP;  // kept entries per phase-2 sweep (8 or 16); each lane then sweeps GRP pixels
 constexpr int PANEL_STRIDE = 33; // float2 row stride of the panel (bank-conflict-free in both phases)
@@ -46,11 +52,6 @@ struct BwdSmem {
   uint32_t smax;
 };
 
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
 __device__ __forceinline__ float xchg_add(float lo, float hi, int off, bool upper) {
   const float send = upper ? lo : hi, mine = upper ? hi : lo;
   return mine + __shfl_xor_sync(0xffffffffu, send, off);
@@ -66,6 +67,11 @@ __device__ __forceinline__ float warp_sum8(const float* v, int lane) {
   y += __shfl_xor_sync(0xffffffffu, y, 2);
   y += __shfl_xor_sync(0xffffffffu, y, 1);
   return y;
+}
+__device__ __forceinline__ float fast_exp(float x) {  // ex2.approx(x log2 e): 2 ulp, enough for gradients
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
+  return r;
 }
 __device__ __forceinline__ float fast_rcp(float x) {
   float r;
@@ -145,14 +151,11 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   float dpix[3] = {0.f, 0.f, 0.f};
   if (inside) { dpix[0] = dL_dpix[pid]; dpix[1] = dL_dpix[HW + pid]; dpix[2] = dL_dpix[2 * HW + pid]; }
   Wp.pix[lane] = make_float4(dpix[0], dpix[1], dpix[2], 0.f);
-  float dpo[K > 0 ? K : 1], acc_o[K > 0 ? K : 1], last_o[K > 0 ? K : 1];
+  float dpo[K > 0 ? K : 1];
 #pragma unroll
-  for (int k = 0; k < (K > 0 ? K : 1); k++) {
-    dpo[k] = (K > 0 && inside) ? dL_dobjpix[k * HW + pid] : 0.f;
-    acc_o[k] = 0.f; last_o[k] = 0.f;
-  }
-  const float bg_dot = bg[0] * dpix[0] + bg[1] * dpix[1] + bg[2] * dpix[2];
-  float acc_r[3] = {0.f, 0.f, 0.f}, last_c[3] = {0.f, 0.f, 0.f}, last_alpha = 0.f;
+  for (int k = 0; k < (K > 0 ? K : 1); k++) dpo[k] = (K > 0 && inside) ? dL_dobjpix[k * HW + pid] : 0.f;
+  // dL/dpixel . (everything blended behind the current entry): starts as the background's share
+  float behind = T_final * (bg[0] * dpix[0] + bg[1] * dpix[1] + bg[2] * dpix[2]);
 
   const uint32_t warp_last = __reduce_max_sync(0xffffffffu, my_last);
   if (tid == 0) M.smax = 0;
@@ -184,18 +187,33 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       const int nk = __popc(mask);
       for (int i = 0; i < nk; i++) {
         const int j = Wp.q[i];
-        const uint32_t pos = top - j;
         const float4 a = S.a[j];
         const float4 b = S.b[j];
+        const uint32_t pos = top - j;
         const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
         const float power = gauss_power(dx, dy, a.z, a.w, b.x);
         bool hit = pos < my_last && !(power > 0.0f || power < b.z);
+#ifdef GSR_BWD_EXACT_EXP
         float G = 0.f, alpha = 0.f;
         if (hit) {
           G = expf(power);
           alpha = fminf(0.99f, fpx::mul(b.y, G));
           hit = !(alpha < 1.0f / 255.0f);
         }
+#else
+        // MUFU.EX2 of the scaled argument (2 instructions instead of expf's 9), evaluated by every lane (no
+        // divergent region).  Whether a pair contributed must be decided exactly as the forward decided it, so
+        // when some lane's alpha lands next to the 1/255 threshold (rare) the warp redoes it with the forward's
+        // arithmetic.
+        float G = fast_exp(power);
+        float alpha = fminf(0.99f, b.y * G);
+        const bool near = hit && fabsf(alpha - 1.0f / 255.0f) < 4e-8f;
+        if (__any_sync(0xffffffffu, near)) {
+          const float Ge = expf(fminf(power, 0.f));
+          if (near) { G = Ge; alpha = fminf(0.99f, fpx::mul(b.y, Ge)); }
+        }
+        hit = hit && !(alpha < 1.0f / 255.0f);
+#endif
         if (!__any_sync(0xffffffffu, hit)) continue;
 #ifdef GSR_STATS
         { const uint32_t hm = __ballot_sync(0xffffffffu, hit); GSR_STAT(3, 1); GSR_STAT(4, __popc(hm)); }
@@ -205,33 +223,24 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 #pragma unroll
         for (int k = 0; k < (K > 0 ? K : 1); k++) vo[k] = 0.f;
         if (hit) {
+          // dC/dalpha_j = T_j c_j - (sum_{k behind j} c_k alpha_k T_k + T_final bg) / (1 - alpha_j); dotted with
+          // dL/dpixel the sum is ONE running scalar `behind` (the reference carries the same quantity per
+          // channel, normalised, as accum_rec: backward.cu:499-521)
           const float4 c = S.c[j];
-          const float col[3] = {b.w, c.x, c.y};
+          float cd = b.w * dpix[0] + c.x * dpix[1] + c.y * dpix[2];
           const float inv = fast_rcp(1.f - alpha);
           T = T * inv;
           wc = alpha * T;
-          const float keep_prev = 1.f - last_alpha;
-          float dL_dalpha = 0.f;
-#pragma unroll
-          for (int ch = 0; ch < 3; ch++) {
-            acc_r[ch] = last_alpha * last_c[ch] + keep_prev * acc_r[ch];
-            last_c[ch] = col[ch];
-            dL_dalpha += (col[ch] - acc_r[ch]) * dpix[ch];
-          }
           if (K > 0) {
             const float* f = obj_feats + (size_t)M.id[j] * K;
 #pragma unroll
             for (int k = 0; k < K; k++) {
-              const float o = __ldg(f + k);
-              acc_o[k] = last_alpha * last_o[k] + keep_prev * acc_o[k];
-              last_o[k] = o;
-              dL_dalpha += (o - acc_o[k]) * dpo[k];
+              cd = fmaf(__ldg(f + k), dpo[k], cd);
               vo[k] = wc * dpo[k];
             }
           }
-          dL_dalpha *= T;
-          last_alpha = alpha;
-          dL_dalpha += (-T_final * inv) * bg_dot;
+          const float dL_dalpha = fmaf(T, cd, -behind * inv);
+          behind = fmaf(cd, wc, behind);
           wg = G * dL_dalpha;
         }
         Wp.panel[ng][lane] = make_float2(wc, wg);
