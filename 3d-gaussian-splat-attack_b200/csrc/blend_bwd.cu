@@ -91,20 +91,33 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
     const int j = Wp.gj[e];
     cx = M.S.a[j].x; cy = M.S.a[j].y; g = M.id[j];
   }
-  const float wyh = wy0f + (float)(h * (GRP / 8));
   const float2* row = &Wp.panel[e][h * GRP];
   const float4* pix = &Wp.pix[h * GRP];
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, m0 = 0.f, m1 = 0.f, m2 = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f;
+  // raw moments of w in the lane's local pixel coordinates (lx = 0..7, r = row inside the lane's strip): the
+  // coordinates are compile-time constants, so each sum is one FFMA/FADD per pixel (none where the factor is 0)
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, M0 = 0.f, Mx = 0.f, My = 0.f, Mxx = 0.f, Mxy = 0.f;
 #pragma unroll
   for (int i = 0; i < GRP; i++) {
     const float2 pr = row[i];
     const float4 dp = pix[i];
-    const float dx = cx - (wx0f + (float)(i & 7)), dy = cy - (wyh + (float)(i >> 3));
+    const int lx = i & 7, r = i >> 3;
     s0 = fmaf(pr.x, dp.x, s0); s1 = fmaf(pr.x, dp.y, s1); s2 = fmaf(pr.x, dp.z, s2);
-    const float wx = pr.y * dx, wy = pr.y * dy;
-    m0 += pr.y; m1 += wx; m2 += wy;
-    mxx = fmaf(wx, dx, mxx); mxy = fmaf(wx, dy, mxy); myy = fmaf(wy, dy, myy);
+    M0 += pr.y;
+    if (lx == 1) { Mx += pr.y; Mxx += pr.y; }
+    if (lx > 1) { Mx = fmaf(pr.y, (float)lx, Mx); Mxx = fmaf(pr.y, (float)(lx * lx), Mxx); }
+    if (r == 1) {
+      My += pr.y;  // r is 0 or 1, so sum w r^2 = sum w r
+      if (lx == 1) Mxy += pr.y;
+      if (lx > 1) Mxy = fmaf(pr.y, (float)lx, Mxy);
+    }
   }
+  // moments about the Gaussian's centre: dx = Dx - lx, dy = Dy - r
+  const float Dx = cx - wx0f, Dy = cy - (wy0f + (float)(h * (GRP / 8)));
+  const float a1 = fmaf(Dx, M0, -Mx), a2 = fmaf(Dy, M0, -My);          // sum w dx, sum w dy
+  float m0 = M0, m1 = a1, m2 = a2;
+  float mxx = fmaf(Dx, a1, fmaf(-Dx, Mx, Mxx));                          // Dx^2 M0 - 2 Dx Mx + Mxx
+  float mxy = fmaf(Dy, a1, fmaf(-Dx, My, Mxy));                          // Dx Dy M0 - Dy Mx - Dx My + Mxy
+  float myy = fmaf(Dy, a2, fmaf(-Dy, My, My));                           // Dy^2 M0 - 2 Dy My + Myy (Myy = My)
 #pragma unroll
   for (int off = GRP; off < 32; off <<= 1) {
     s0 += __shfl_xor_sync(0xffffffffu, s0, off); s1 += __shfl_xor_sync(0xffffffffu, s1, off);

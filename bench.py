@@ -122,7 +122,13 @@ def cameras_for(scene, n_total):
 def cpu_views_per_sec(scene, cams, steps, warmup, views):
     """Times the CPU oracle (the reference's rasterizer math restated for the host, oracle/cpu_ref.cpp;
     the reference has no CPU implementation of its own) on `views` views per step."""
-    from oracle.cpu_ref import Oracle, num_threads
+    from oracle.cpu_ref import Oracle, num_threads, set_num_threads
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm is meant to use every host core
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    set_num_threads(avail)
     cores = num_threads()
     dL = scene["dL_dpix"]
 
