@@ -115,8 +115,10 @@ struct SortTemp {
     hist = c.take<uint32_t>(SORT_MAX_PASSES * 256);
     tickets = c.take<uint32_t>(64);
     status_off = c.off;
-    pass_stride = (size_t)sort_tiles(n) * 256 * sizeof(uint32_t);
-    status = c.take<uint32_t>((size_t)SORT_MAX_PASSES * sort_tiles(n) * 256);
+    // 32-bit look-back words below 2^30 pairs, 64-bit words above (radix_sort.cu)
+    const size_t word = n >= ((int64_t)1 << 30) ? 8 : 4;
+    pass_stride = (size_t)sort_tiles(n) * 256 * word;
+    status = (uint32_t*)c.take<char>((size_t)SORT_MAX_PASSES * pass_stride);
     bytes = c.off;
   }
   // prefix of the buffer that must be zeroed before a sort of `passes` passes

@@ -17,7 +17,16 @@
 namespace gsr {
 namespace {
 
-constexpr uint32_t ST_AGG = 1u << 30, ST_PREFIX = 1u << 31, ST_MASK = (1u << 30) - 1;
+// Look-back status word = 2 flag bits + a count.  32-bit words (30-bit counts) serve n < 2^30; larger sorts
+// (up to the 2^32 pairs the reference's u32 offsets allow) use 64-bit words.
+template <typename W> struct St;
+template <> struct St<uint32_t> {
+  static constexpr uint32_t AGG = 1u << 30, PREFIX = 1u << 31, MASK = (1u << 30) - 1;
+};
+template <> struct St<unsigned long long> {
+  static constexpr unsigned long long AGG = 1ull << 62, PREFIX = 1ull << 63, MASK = (1ull << 62) - 1;
+};
+constexpr int64_t SORT_SMALL_LIMIT = (int64_t)1 << 30;
 constexpr int NWARPS = SORT_THREADS / 32;
 
 template <typename KeyT>
@@ -70,12 +79,13 @@ struct PassSmem {
   uint32_t tile;
 };
 
-template <typename KeyT>
+template <typename KeyT, typename W>
 __global__ void __launch_bounds__(SORT_THREADS)
 onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, int64_t n, int shift,
-                     uint32_t digit_mask, const uint32_t* __restrict__ digit_base, uint32_t* status,
+                     uint32_t digit_mask, const uint32_t* __restrict__ digit_base, W* status,
                      uint32_t* ticket) {
+  constexpr W ST_AGG = St<W>::AGG, ST_PREFIX = St<W>::PREFIX, ST_MASK = St<W>::MASK;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   PassSmem<KeyT>& S = *reinterpret_cast<PassSmem<KeyT>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -123,9 +133,9 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     S.warp_hist[w][tid] = count;
     count += c;
   }
-  volatile uint32_t* st = status;
-  if (tile == 0) st[tid] = ST_PREFIX | count;
-  else st[(size_t)tile * 256 + tid] = ST_AGG | count;
+  volatile W* st = status;
+  if (tile == 0) st[tid] = ST_PREFIX | (W)count;
+  else st[(size_t)tile * 256 + tid] = ST_AGG | (W)count;
   // exclusive scan of `count` over the 256 digits
   uint32_t incl = count;
 #pragma unroll
@@ -146,22 +156,22 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     // flag and value, so no fence is needed around it
     int64_t j = (int64_t)tile - 1;
     while (true) {
-      uint32_t w[4];
+      W w[4];
 #pragma unroll
-      for (int k = 0; k < 4; k++) { w[k] = 1u << 31; if (j - k >= 0) w[k] = st[(size_t)(j - k) * 256 + tid]; }
+      for (int k = 0; k < 4; k++) { w[k] = ST_PREFIX; if (j - k >= 0) w[k] = st[(size_t)(j - k) * 256 + tid]; }
       bool done = false, stop = false;
       int adv = 0;
 #pragma unroll
       for (int k = 0; k < 4; k++) {
         if (!done && !stop) {
           if ((w[k] & (ST_AGG | ST_PREFIX)) == 0) stop = true;
-          else { excl += w[k] & ST_MASK; adv = k + 1; done = (w[k] & ST_PREFIX) != 0; }
+          else { excl += (uint32_t)(w[k] & ST_MASK); adv = k + 1; done = (w[k] & ST_PREFIX) != 0; }
         }
       }
       if (done) break;
       j -= adv;
     }
-    st[(size_t)tile * 256 + tid] = ST_PREFIX | ((excl + count) & ST_MASK);
+    st[(size_t)tile * 256 + tid] = ST_PREFIX | ((W)(excl + count) & ST_MASK);
   }
   S.global_base[tid] = (int32_t)(digit_base[tid] + excl) - (int32_t)doff;
   __syncthreads();
@@ -199,7 +209,7 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
   if (passes < 1 || passes > (int)sizeof(KeyT) || passes > SORT_MAX_PASSES) {
     set_error("sort: end_bit %d out of range", end_bit); return GSR_ERR_INVALID;
   }
-  if (n >= (int64_t)ST_MASK) { set_error("sort: %lld pairs exceed the 2^30 limit", (long long)n); return GSR_ERR_INVALID; }
+  if (n >= ((int64_t)1 << 32)) { set_error("sort: %lld pairs exceed the 2^32 limit", (long long)n); return GSR_ERR_INVALID; }
   if (n == 0) return GSR_OK;
   SortTemp T(temp, n);
   if (!hist_ready) {  // otherwise the caller zeroed `temp` and the producer of keys0 filled T.hist (sort_prepare)
@@ -210,18 +220,25 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
   }
   sort_scan_hist_kernel<<<1, 32 * SORT_MAX_PASSES, 0, st>>>(T.hist, passes);
   GSR_LAUNCH_CHECK("sort_scan_hist_kernel");
-  GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(PassSmem<KeyT>)));
   const int64_t tiles = sort_tiles(n);
+  const bool big = n >= SORT_SMALL_LIMIT;
+  if (big) GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT, unsigned long long>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PassSmem<KeyT>)));
+  else GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT, uint32_t>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PassSmem<KeyT>)));
   for (int p = 0; p < passes; p++) {
     const int shift = 8 * p, nb = end_bit - shift < 8 ? end_bit - shift : 8;
     const KeyT* kin = (p & 1) ? keys1 : keys0;
     KeyT* kout = (p & 1) ? keys0 : keys1;
     const uint32_t* vin = (p & 1) ? vals1 : vals0;
     uint32_t* vout = (p & 1) ? vals0 : vals1;
-    onesweep_pass_kernel<KeyT><<<(unsigned)tiles, SORT_THREADS, sizeof(PassSmem<KeyT>), st>>>(
-        kin, kout, vin, vout, n, shift, (1u << nb) - 1, T.hist + p * 256, T.status + (size_t)p * tiles * 256,
-        T.tickets + p);
+    char* stp = (char*)T.status + (size_t)p * T.pass_stride;
+    if (big)
+      onesweep_pass_kernel<KeyT, unsigned long long><<<(unsigned)tiles, SORT_THREADS, sizeof(PassSmem<KeyT>), st>>>(
+          kin, kout, vin, vout, n, shift, (1u << nb) - 1, T.hist + p * 256, (unsigned long long*)stp, T.tickets + p);
+    else
+      onesweep_pass_kernel<KeyT, uint32_t><<<(unsigned)tiles, SORT_THREADS, sizeof(PassSmem<KeyT>), st>>>(
+          kin, kout, vin, vout, n, shift, (1u << nb) - 1, T.hist + p * 256, (uint32_t*)stp, T.tickets + p);
     GSR_LAUNCH_CHECK("onesweep_pass_kernel");
   }
   return GSR_OK;
