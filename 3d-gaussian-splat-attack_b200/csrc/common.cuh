@@ -99,7 +99,10 @@ struct Image {
 
 // ---- radix sort geometry ---------------------------------------------------------------------
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
+#ifndef GSR_SORT_ITEMS
+#define GSR_SORT_ITEMS 16
+#endif
+constexpr int SORT_ITEMS = GSR_SORT_ITEMS;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 pairs per block
 constexpr int SORT_MAX_PASSES = 8;
 inline int64_t sort_tiles(int64_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }

@@ -79,8 +79,11 @@ struct PassSmem {
   uint32_t tile;
 };
 
+#ifndef GSR_SORT_MINBLOCKS
+#define GSR_SORT_MINBLOCKS 3
+#endif
 template <typename KeyT, typename W>
-__global__ void __launch_bounds__(SORT_THREADS)
+__global__ void __launch_bounds__(SORT_THREADS, GSR_SORT_MINBLOCKS)
 onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, int64_t n, int shift,
                      uint32_t digit_mask, const uint32_t* __restrict__ digit_base, W* status,
