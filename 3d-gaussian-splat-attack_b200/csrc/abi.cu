@@ -249,6 +249,30 @@ int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, c
   return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
 }
 
+int gsr_pgd_linf_update(float* param, const float* grad, const float* orig, int64_t n, float alpha, float epsilon,
+                        void* stream) {
+  if (n < 0 || (n > 0 && (!param || !grad || !orig))) { set_error("pgd_linf_update: bad arguments"); return GSR_ERR_INVALID; }
+  return launch_pgd_linf(param, grad, orig, n, alpha, epsilon, (cudaStream_t)stream);
+}
+
+int gsr_pgd_l2_update(float* param, const float* grad, const float* orig, int64_t rows, int32_t width, float alpha,
+                      float epsilon, double* scratch8, void* stream) {
+  if (rows < 0 || width < 0 || (rows * width > 0 && (!param || !grad || !orig || !scratch8))) {
+    set_error("pgd_l2_update: bad arguments"); return GSR_ERR_INVALID;
+  }
+  return launch_pgd_l2(param, grad, orig, rows, width, alpha, epsilon, scratch8, (cudaStream_t)stream);
+}
+
+int gsr_image_to_u8_hwc(const float* chw, uint8_t* hwc, int32_t W, int32_t H, void* stream) {
+  if (W < 0 || H < 0 || ((int64_t)W * H > 0 && (!chw || !hwc))) { set_error("image_to_u8_hwc: bad arguments"); return GSR_ERR_INVALID; }
+  return launch_image_u8_hwc(chw, hwc, W, H, (cudaStream_t)stream);
+}
+
+int gsr_detector_scale(const float* x, float* y, const float* dL_dy, float* dL_dx, int64_t n, void* stream) {
+  if (n < 0 || (n > 0 && (!x || (!y && !dL_dx) || (dL_dx && !dL_dy)))) { set_error("detector_scale: bad arguments"); return GSR_ERR_INVALID; }
+  return launch_detector_scale(x, y, dL_dy, dL_dx, n, (cudaStream_t)stream);
+}
+
 int gsr_sort_pairs_u64(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
                        int64_t n, int32_t end_bit, void* temp, size_t temp_bytes, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;

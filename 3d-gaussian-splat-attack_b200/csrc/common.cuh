@@ -195,6 +195,11 @@ int launch_preprocess_bwd(const gsr_inputs& in, const Geom& g, const int32_t* ra
                           float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
                           float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, bool accumulate,
                           cudaStream_t st);
+int launch_pgd_linf(float* p, const float* g, const float* p0, int64_t n, float alpha, float eps, cudaStream_t st);
+int launch_pgd_l2(float* p, const float* g, const float* p0, int64_t rows, int width, float alpha, float eps,
+                  double* sumsq_scratch, cudaStream_t st);
+int launch_image_u8_hwc(const float* chw, uint8_t* hwc, int W, int H, cudaStream_t st);
+int launch_detector_scale(const float* x, float* y, const float* dy, float* dx, int64_t n, cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 
 uint32_t higher_msb(uint32_t n);

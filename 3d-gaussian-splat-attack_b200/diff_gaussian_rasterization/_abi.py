@@ -45,6 +45,11 @@ EXPORTS = {
                                C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p] + [C.c_void_p] * 9 + [C.c_void_p]),
     "gsr_backward_accumulate": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_size_t, C.c_void_p] + [C.c_void_p] * 8 + [C.c_void_p]),
+    "gsr_pgd_linf_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p]),
+    "gsr_pgd_l2_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_float,
+                                    C.c_void_p, C.c_void_p]),
+    "gsr_image_to_u8_hwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "gsr_detector_scale": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "gsr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_sort_pairs_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),

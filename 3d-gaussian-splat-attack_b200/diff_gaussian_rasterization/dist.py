@@ -12,7 +12,7 @@ from typing import Callable, Dict, Iterable, List, Optional, Sequence
 import torch
 import torch.distributed as dist
 
-__all__ = ["shard_views", "FlatGradBucket", "sharded_step"]
+__all__ = ["shard_views", "FlatGradBucket", "sharded_step", "sharded_accumulate_step", "backprop_inputs"]
 
 
 def shard_views(n_views: int, rank: int, world: int) -> List[int]:
@@ -31,13 +31,16 @@ class FlatGradBucket:
     and `all_reduce()` is a single collective over it.
     """
 
-    def __init__(self, params: Dict[str, torch.Tensor]):
+    def __init__(self, params: Dict[str, torch.Tensor], bind: bool = True):
+        """bind=False: only lay the buffer out after `params` (any tensors, e.g. activations); nothing is attached
+        to .grad -- for the accumulate API (sharded_accumulate_step), which writes the slices itself."""
         if not params:
             raise ValueError("no parameters")
         ps = list(params.values())
         dev, dt = ps[0].device, ps[0].dtype
+        self.bind = bind
         for n, p in params.items():
-            if not p.is_leaf or not p.requires_grad:
+            if bind and (not p.is_leaf or not p.requires_grad):
                 raise ValueError(f"{n}: must be a leaf tensor that requires grad")
             if p.device != dev or p.dtype != dt:
                 raise ValueError(f"{n}: all parameters must share device and dtype")
@@ -48,11 +51,14 @@ class FlatGradBucket:
         off = 0
         for n, p in self.params.items():
             self.slices[n] = (off, off + p.numel())
-            p.grad = self.flat[off:off + p.numel()].view(p.shape)
+            if bind:
+                p.grad = self.flat[off:off + p.numel()].view(p.shape)
             off += p.numel()
 
     def zero(self):
         self.flat.zero_()
+        if not self.bind:
+            return
         for n, p in self.params.items():  # re-bind in case an optimizer step replaced .grad (set_to_none=True)
             a, b = self.slices[n]
             if p.grad is None or p.grad.data_ptr() != self.flat.data_ptr() + a * self.flat.element_size():
@@ -95,3 +101,65 @@ def sharded_step(views: Sequence, render_backward: Callable[[object], Optional[t
     if on and world > 1:
         dist.all_reduce(total, op=dist.ReduceOp.SUM, group=group)
     return total
+
+
+def sharded_accumulate_step(settings: Sequence, inputs: Dict[str, torch.Tensor],
+                            loss_fn: Callable[[torch.Tensor, int], torch.Tensor], bucket: FlatGradBucket,
+                            rank: Optional[int] = None, world: Optional[int] = None, group=None,
+                            forward_view=None, backward_view=None) -> torch.Tensor:
+    """One multi-camera gradient step on the view-level accumulate API (views.forward_view / backward_view).
+
+    `settings[k]` is the GaussianRasterizationSettings of camera k; `inputs` maps the rasterizer's argument names
+    (means3D, opacities, shs | colors_precomp, scales + rotations | cov3D_precomp) to the tensors render() would
+    pass (gaussian_renderer/__init__.py:86-95).  For each of this rank's cameras the view is rendered without an
+    autograd graph, `loss_fn(image, k)` is differentiated w.r.t. the image only, and the rasterizer's backward adds
+    the attribute gradients straight into the bucket (bucket.params must be keyed like `inputs`).  Then ONE
+    all-reduce.  Returns the loss summed over all cameras and ranks.
+
+    When the inputs are activations of raw parameters (sigmoid / exp / normalize, scene/gaussian_model.py:97-121)
+    call `backprop_inputs(inputs, bucket)` afterwards: the activation backward then runs once per step instead of
+    once per camera.
+    """
+    if forward_view is None or backward_view is None:
+        from . import views as _v
+        forward_view, backward_view = forward_view or _v.forward_view, backward_view or _v.backward_view
+    on = dist.is_available() and dist.is_initialized()
+    rank = (dist.get_rank(group) if on else 0) if rank is None else rank
+    world = (dist.get_world_size(group) if on else 1) if world is None else world
+    if set(bucket.params) != set(inputs):
+        raise ValueError(f"bucket is keyed {sorted(bucket.params)}, inputs {sorted(inputs)}")
+    bucket.zero()
+    grads = {n: bucket.grad(n) for n in inputs}
+    plain = {n: t.detach() for n, t in inputs.items()}
+    total = torch.zeros((), dtype=bucket.flat.dtype, device=bucket.flat.device)
+    for k in shard_views(len(settings), rank, world):
+        image, _radii, state = forward_view(settings[k], plain["means3D"], plain["opacities"],
+                                            **{n: t for n, t in plain.items() if n not in ("means3D", "opacities")})
+        image = image.detach().requires_grad_(True)
+        loss = loss_fn(image, k)
+        (dL_dimage,) = torch.autograd.grad(loss, image)
+        backward_view(state, dL_dimage, grads)
+        total = total + loss.detach().to(total.dtype)
+    bucket.all_reduce(group)
+    if on and world > 1:
+        dist.all_reduce(total, op=dist.ReduceOp.SUM, group=group)
+    return total
+
+
+def backprop_inputs(inputs: Dict[str, torch.Tensor], bucket: FlatGradBucket) -> None:
+    """Chain the bucket's gradients (w.r.t. `inputs`) back to the leaves: inputs computed from raw parameters
+    (sigmoid / exp / normalize ...) are back-propagated with ONE autograd call; inputs that are leaves themselves
+    get .grad set to (or incremented by) their bucket slice."""
+    ts, gs = [], []
+    for n, t in inputs.items():
+        if not t.requires_grad:
+            continue
+        if t.grad_fn is not None:
+            ts.append(t)
+            gs.append(bucket.grad(n))
+        elif t.grad is None:
+            t.grad = bucket.grad(n)
+        elif t.grad.data_ptr() != bucket.grad(n).data_ptr():
+            t.grad += bucket.grad(n)
+    if ts:
+        torch.autograd.backward(ts, gs)

@@ -118,6 +118,23 @@ int gsr_backward_accumulate(const gsr_inputs* in, const void* geom, const int32_
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);
 
+/* ---- the elementwise steps either side of the rasterizer in an attack iteration ----
+ * PGD updates of one attribute tensor, in place (attack.py:25-173).  `orig` is the un-attacked copy.
+ *   L-inf (gaussian_*_linf_attack):  p <- clamp(p - alpha sign(g) - orig, -eps, eps) + orig, rounded like the torch
+ *                                    op sequence it replaces.
+ *   L2   (gaussian_*_l2_attack):     p <- p - alpha g/||g||_2 (no step if the norm is 0); each row (one Gaussian,
+ *                                    `width` floats) of p - orig longer than eps is scaled by eps/(len + 1e-7)
+ *                                    (Tensor.renorm(2, 0, eps)); p <- orig + that.  scratch8 = 8 device bytes. */
+int gsr_pgd_linf_update(float* param, const float* grad, const float* orig, int64_t n, float alpha, float epsilon,
+                        void* stream);
+int gsr_pgd_l2_update(float* param, const float* grad, const float* orig, int64_t rows, int32_t width, float alpha,
+                      float epsilon, double* scratch8, void* stream);
+/* Image hand-off to the detector: uint8 HWC = byte(clamp(x,0,1)*255) of a float CHW render (attack.py:438-443,
+ * :538-543); y = clip(x*255 + 0.5, 0, 255) and/or dL/dx = 255 dL/dy inside the clip range
+ * (detectors/detectron2_detector.py:78).  In gsr_detector_scale pass y = NULL or dL_dx = NULL to skip that half. */
+int gsr_image_to_u8_hwc(const float* chw, uint8_t* hwc, int32_t W, int32_t H, void* stream);
+int gsr_detector_scale(const float* x, float* y, const float* dL_dy, float* dL_dx, int64_t n, void* stream);
+
 /* ---- stage-level entry points (parity tests and per-stage roofline timing) ---- */
 
 /* Stable LSD radix sort of (u64 key, u32 value) pairs on bits [0, end_bit); replaces

@@ -108,3 +108,67 @@ def test_bucket_binds_grads_and_rebinds_after_set_to_none():
     assert b.all_reduce() is None  # no process group: no-op
     with pytest.raises(ValueError):
         FlatGradBucket({"a": torch.zeros(3)})
+
+
+# ---------------------------------------------------------------- accumulate-API step (views.forward_view / backward_view)
+def _fake_view_api():
+    """Stand-in for views.forward_view / backward_view on CPU: image = a fixed linear map of sin(inputs), whose
+    backward ADDS into the given buffers (like gsr_backward_accumulate)."""
+    def fwd(rs, means3D, opacities, shs=None, scales=None, rotations=None):
+        ins = dict(means3D=means3D, opacities=opacities, shs=shs, scales=scales, rotations=rotations)
+        img = sum(((t * rs[i]).sin() * (i + 1)).sum() for i, t in enumerate(ins.values())) * torch.ones(3, 2, 2)
+        return img, None, (rs, ins)
+
+    def bwd(state, dL_dimage, grads):
+        rs, ins = state
+        s = dL_dimage.sum()
+        for i, (n, t) in enumerate(ins.items()):
+            grads[n] += s * (i + 1) * rs[i] * (t * rs[i]).cos()
+    return fwd, bwd
+
+
+def _acc_inputs():
+    raw = _make_params(seed=4)
+    raw = {"means3D": raw["xyz"], "opacities": raw["opacity"], "shs": raw["shs"], "scales": raw["scales"],
+           "rotations": raw["rotations"]}
+    # activations as in scene/gaussian_model.py:97-121
+    act = {"means3D": raw["means3D"], "opacities": torch.sigmoid(raw["opacities"]), "shs": raw["shs"],
+           "scales": torch.exp(raw["scales"]), "rotations": torch.nn.functional.normalize(raw["rotations"])}
+    return raw, act
+
+
+def _acc_worker(rank, world, port, n_views, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from diff_gaussian_rasterization.dist import FlatGradBucket, sharded_accumulate_step, backprop_inputs
+        raw, act = _acc_inputs()
+        bucket = FlatGradBucket(act, bind=False)
+        fwd, bwd = _fake_view_api()
+        total = sharded_accumulate_step(_views(n_views), act, lambda img, k: (img * (k + 1)).sum(), bucket,
+                                        forward_view=fwd, backward_view=bwd)
+        backprop_inputs(act, bucket)
+        out[rank] = (bucket.flat.clone(), float(total), {n: p.grad.clone() for n, p in raw.items()})
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_accumulate_step_matches_autograd_reference():
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "3d-gaussian-splat-attack_b200"))
+    n_views = 5
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_acc_worker, args=(2, _free_port(), n_views, out), nprocs=2, join=True)
+    # reference: plain autograd through the same fake renderer, one process
+    raw, act = _acc_inputs()
+    fwd, _ = _fake_view_api()
+    loss = sum((fwd(v, **act)[0] * (k + 1)).sum() for k, v in enumerate(_views(n_views)))
+    loss.backward()
+    f0, t0, g0 = out[0]
+    f1, t1, g1 = out[1]
+    assert torch.equal(f0, f1) and t0 == t1
+    assert abs(t0 - float(loss)) <= 1e-4 * abs(float(loss))
+    for n, p in raw.items():
+        assert torch.allclose(g0[n], p.grad, rtol=1e-4, atol=1e-5), n
+        assert torch.equal(g0[n], g1[n])

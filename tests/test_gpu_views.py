@@ -122,3 +122,67 @@ def test_backward_view_argument_errors():
         views.backward_view(st, dL, dict(means3D=torch.zeros_like(t["means3D"]), opacities=torch.zeros_like(t["opacities"])))
     with pytest.raises(Exception):
         views.backward_view(st, dL, dict(bogus=torch.zeros(1, device="cuda")))
+
+
+def test_attack_iteration_accumulate_path_matches_reference_style_autograd_loop():
+    """One DAGGER-style iteration (attack.py:463-530): raw parameters -> activations -> render 3 cameras -> loss ->
+    gradients of the RAW parameters -> L-inf PGD step.  The accumulate path (dist.sharded_accumulate_step +
+    backprop_inputs + attack_ops) must land on the parameters the reference-style loop (GaussianRasterizer + autograd
+    + the torch update sequence) lands on."""
+    import diff_gaussian_rasterization as dgr
+    from diff_gaussian_rasterization import attack_ops as ao
+    from diff_gaussian_rasterization.dist import FlatGradBucket, sharded_accumulate_step, backprop_inputs
+    from gsr_synth import ring_cameras
+    s = h.make_scene("tiny")
+    cams = ring_cameras(3, width=160, height=120)
+    settings = []
+    for c in cams:
+        sc = dict(s); sc["cam"] = c
+        settings.append(h.settings_for(sc))
+    rng = np.random.default_rng(11)
+    targets = [torch.from_numpy(rng.random((3, 120, 160)).astype(np.float32)).cuda() for _ in cams]
+    loss_fn = lambda img, k: ((img - targets[k]) ** 2).sum()
+
+    def raw_params():
+        t = h.scene_tensors(s, requires_grad=False)
+        raw = dict(xyz=t["means3D"].clone(), f=t["shs"].clone(), opacity=torch.logit(t["opacities"].clamp(1e-4, 1 - 1e-4)),
+                   scaling=torch.log(t["scales"]), rotation=t["rotations"] * 1.7)
+        return {k: v.requires_grad_(True) for k, v in raw.items()}
+
+    def activate(raw):
+        return dict(means3D=raw["xyz"], opacities=torch.sigmoid(raw["opacity"]), shs=raw["f"],
+                    scales=torch.exp(raw["scaling"]), rotations=torch.nn.functional.normalize(raw["rotation"]))
+
+    # reference-style loop
+    A = raw_params()
+    orig = {k: v.detach().clone() for k, v in A.items()}
+    act = activate(A)
+    loss = 0
+    for k, rs in enumerate(settings):
+        m2 = torch.zeros((s["P"], 3), device="cuda", requires_grad=True)
+        img, _ = dgr.GaussianRasterizer(rs)(means3D=act["means3D"], means2D=m2, opacities=act["opacities"], shs=act["shs"],
+                                            scales=act["scales"], rotations=act["rotations"])
+        loss = loss + loss_fn(img, k)
+    loss.backward()
+    with torch.no_grad():
+        for k, p in A.items():
+            eta = 0.01 * torch.sign(p.grad)
+            eta.mul_(-1)
+            p.add_(eta)
+            p.sub_(orig[k]).clamp_(-0.05, 0.05).add_(orig[k])
+    # accumulate path
+    B = raw_params()
+    actB = activate(B)
+    bucket = FlatGradBucket(actB, bind=False)
+    total = sharded_accumulate_step(settings, actB, loss_fn, bucket, rank=0, world=1)
+    backprop_inputs(actB, bucket)
+    assert abs(float(total) - float(loss)) <= 1e-5 * abs(float(loss))
+    for k in A:
+        ok, worst = h.grad_close(B[k].grad.cpu().numpy(), A[k].grad.cpu().numpy())
+        assert ok, (k, worst)
+    ao.pgd_step_(B, {k: v.grad.contiguous() for k, v in B.items()}, orig, 0.01, 0.05, norm="linf")
+    for k in A:
+        # sign() of a gradient that is ~0 may differ between two summation orders: allow it on a tiny fraction
+        diff = (A[k].detach() - B[k].detach()).abs()
+        assert float((diff > 1e-6).float().mean()) < 2e-3, k
+        assert float(diff.max()) <= 2 * 0.01 + 1e-6
