@@ -489,13 +489,18 @@ def run_gsr(args):
         return
     top = max(stages, key=lambda k: stages[k]["ms"])
     t = stages[top]
+    traffic = None  # dram bytes / launch of the dominant kernel from the committed ncu --set full capture
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))[top]["dram_bytes_per_launch"]
+    except Exception:
+        pass
     if t["bound"] == "hbm":
         roofline = {"kernel": top, "bound": "hbm", "achieved": t["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s",
-                    "frac": t["hbm_frac"], "traffic": None, "peak_source": peak_src}
+                    "frac": t["hbm_frac"], "traffic": traffic, "peak_source": peak_src}
     else:
         fp32_peak_t = 148 * 128 * sm_max * 1e6 / 1e12
         roofline = {"kernel": top, "bound": "fp32-issue", "achieved": t["fp32_frac"] * fp32_peak_t, "peak": fp32_peak_t,
-                    "unit": "T lane-instr/s", "frac": t["fp32_frac"], "traffic": None,
+                    "unit": "T lane-instr/s", "frac": t["fp32_frac"], "traffic": traffic,
                     "hbm_view": {"achieved": t["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": t["hbm_frac"]},
                     "peak_source": "148 SM x 128 FP32 lanes x sm_max_mhz; HBM " + peak_src}
     c = wl.scene["cam"]
