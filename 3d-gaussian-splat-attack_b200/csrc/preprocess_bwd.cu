@@ -83,6 +83,18 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
   if (ACC && !live) return;
   const int M = in.M;
 
+#ifndef GSR_PREB_NO_HOIST
+  // the SH row is the largest read of this kernel: start it first
+  float shv[48];
+  if (live && in.shs && M == 16) {
+    const float4* sp0 = reinterpret_cast<const float4*>(in.shs) + (size_t)idx * 12;
+#pragma unroll
+    for (int k = 0; k < 12; k++) {
+      const float4 t = __ldg(sp0 + k);
+      shv[4 * k] = t.x; shv[4 * k + 1] = t.y; shv[4 * k + 2] = t.z; shv[4 * k + 3] = t.w;
+    }
+  }
+#endif
   float4 a0 = make_float4(0, 0, 0, 0), a1 = a0;
   float a8 = 0.f;
   if (live) {
@@ -183,12 +195,17 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
       if (M == 16) {
         const float4* sp = reinterpret_cast<const float4*>(in.shs) + (size_t)idx * 12;
         float4* dp = reinterpret_cast<float4*>(dL_dsh) + (size_t)idx * 12;
-        float shv[48], outv[48];
+        float outv[48];
+#ifdef GSR_PREB_NO_HOIST
+        float shv[48];
 #pragma unroll
         for (int k = 0; k < 12; k++) {
           const float4 t = __ldg(sp + k);
           shv[4 * k] = t.x; shv[4 * k + 1] = t.y; shv[4 * k + 2] = t.z; shv[4 * k + 3] = t.w;
         }
+#else
+        (void)sp;
+#endif
 #pragma unroll
         for (int k = 0; k < 48; k++) outv[k] = 0.f;
         ddir = sh_backward(in.D, x, y, z, dRGB, [&](int i) { return V3{shv[3 * i], shv[3 * i + 1], shv[3 * i + 2]}; },
