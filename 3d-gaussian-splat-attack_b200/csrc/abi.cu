@@ -148,18 +148,10 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   return GSR_OK;
 }
 
-int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, uint32_t* point_list,
-                       void* image, void* scratch, size_t scratch_bytes, float* out_color, float* out_objects,
-                       void* stream) {
-  GSR_TRY(check_inputs(in));
-  cudaStream_t st = (cudaStream_t)stream;
-  if (!image || !out_color || (in->K > 0 && !out_objects) || L < 0) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
-  const size_t HW = (size_t)in->W * in->H;
-  if (in->P == 0) {  // rasterize_points.cu:68,81: zero-filled image, nothing launched
-    GSR_CUDA_CHECK(cudaMemsetAsync(out_color, 0, 3 * HW * sizeof(float), st));
-    if (in->K > 0) GSR_CUDA_CHECK(cudaMemsetAsync(out_objects, 0, in->K * HW * sizeof(float), st));
-    return GSR_OK;
-  }
+static int forward_binning_impl(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
+                                uint32_t* point_list, void* image, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  if (!image || L < 0) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  if (in->P == 0) return GSR_OK;
   if (!geom || !radii || !scratch || (L > 0 && !point_list)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
   if (scratch_bytes < Scratch(nullptr, in->P, L).bytes) {
     set_error("scratch too small: need %zu bytes for L=%lld", Scratch(nullptr, in->P, L).bytes, (long long)L);
@@ -189,10 +181,44 @@ int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* ra
     GSR_TRY(debug_sync(in, st, "sort"));
   }
   { StageScope ps(ST_RANGES, st); GSR_TRY(launch_tile_ranges(L, s.tkeys_a, im.ranges, gx * gy, st)); }
-  GSR_TRY(debug_sync(in, st, "tile_ranges"));
+  return debug_sync(in, st, "tile_ranges");
+}
+
+static int forward_blend_impl(const gsr_inputs* in, const void* geom, const uint32_t* point_list, void* image,
+                              float* out_color, float* out_objects, cudaStream_t st) {
+  if (!image || !out_color || (in->K > 0 && !out_objects)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  const size_t HW = (size_t)in->W * in->H;
+  if (in->P == 0) {  // rasterize_points.cu:68,81: zero-filled image, nothing launched
+    GSR_CUDA_CHECK(cudaMemsetAsync(out_color, 0, 3 * HW * sizeof(float), st));
+    if (in->K > 0) GSR_CUDA_CHECK(cudaMemsetAsync(out_objects, 0, in->K * HW * sizeof(float), st));
+    return GSR_OK;
+  }
+  if (!geom) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  Geom g(const_cast<void*>(geom), in->P);
+  Image im(image, in->W, in->H);
   { StageScope ps(ST_BLEND_FWD, st); GSR_TRY(launch_blend_fwd(*in, g, im, point_list, out_color, out_objects, st)); }
-  GSR_TRY(debug_sync(in, st, "blend_fwd"));
-  return GSR_OK;
+  return debug_sync(in, st, "blend_fwd");
+}
+
+int gsr_forward_binning(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, uint32_t* point_list,
+                        void* image, void* scratch, size_t scratch_bytes, void* stream) {
+  GSR_TRY(check_inputs(in));
+  return forward_binning_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+int gsr_forward_blend(const gsr_inputs* in, const void* geom, const uint32_t* point_list, void* image,
+                      float* out_color, float* out_objects, void* stream) {
+  GSR_TRY(check_inputs(in));
+  return forward_blend_impl(in, geom, point_list, image, out_color, out_objects, (cudaStream_t)stream);
+}
+
+int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, uint32_t* point_list,
+                       void* image, void* scratch, size_t scratch_bytes, float* out_color, float* out_objects,
+                       void* stream) {
+  GSR_TRY(check_inputs(in));
+  if (!out_color || (in->K > 0 && !out_objects)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  GSR_TRY(forward_binning_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, (cudaStream_t)stream));
+  return forward_blend_impl(in, geom, point_list, image, out_color, out_objects, (cudaStream_t)stream);
 }
 
 static int backward_impl(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,

@@ -41,6 +41,10 @@ EXPORTS = {
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_forward_render": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsr_forward_binning": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_size_t, C.c_void_p]),
+    "gsr_forward_blend": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
     "gsr_backward": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p] + [C.c_void_p] * 9 + [C.c_void_p]),
     "gsr_backward_accumulate": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,

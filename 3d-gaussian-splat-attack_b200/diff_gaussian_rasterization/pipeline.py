@@ -48,7 +48,7 @@ class _Slot:
 
 class HostStepPipeline:
     def __init__(self, P: int, M: int, W: int, H: int, n_views: int, tanfovx: float, tanfovy: float, sh_degree: int,
-                 device, bg: Optional[torch.Tensor] = None, depth: int = 2, group=None):
+                 device, bg: Optional[torch.Tensor] = None, depth: int = 2, group=None, overlap: bool = True):
         if depth < 1:
             raise ValueError("depth must be >= 1")
         self.P, self.M, self.W, self.H, self.n_views = P, M, W, H, n_views
@@ -61,6 +61,7 @@ class HostStepPipeline:
         self.s_in = torch.cuda.Stream(self.dev)
         self.s_out = torch.cuda.Stream(self.dev)
         self.group = group
+        self.views = _views.ViewPipeline(self.dev, overlap=overlap)
         self.n_submitted = 0
         self.staged = None  # slot whose inputs are in flight and whose compute has not been issued yet
         self.h2d_bytes = 4 * (self.n_param + n_views * 36 + n_views * 3 * H * W)
@@ -83,15 +84,15 @@ class HostStepPipeline:
             cur.wait_event(slot.ev_out)  # the previous gradients of this slot have left
         slot.grad.zero_()
         p = slot.p
+        settings = []
         for v in range(self.n_views):
             cm = slot.cam[v]
-            rs = GaussianRasterizationSettings(
+            settings.append(GaussianRasterizationSettings(
                 image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=self.bg,
                 scale_modifier=1.0, viewmatrix=cm[0:16].view(4, 4), projmatrix=cm[16:32].view(4, 4),
-                sh_degree=self.sh_degree, campos=cm[32:35], prefiltered=False, debug=False)
-            _, _, st = _views.forward_view(rs, p["means3D"], p["opacities"], shs=p["shs"], scales=p["scales"],
-                                           rotations=p["rotations"])
-            _views.backward_view(st, slot.dL[v], slot.g)
+                sh_degree=self.sh_degree, campos=cm[32:35], prefiltered=False, debug=False))
+        self.views.step(settings, lambda img, k: slot.dL[k], slot.g, p["means3D"], p["opacities"], shs=p["shs"],
+                        scales=p["scales"], rotations=p["rotations"])
         if self.group is not False:
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:

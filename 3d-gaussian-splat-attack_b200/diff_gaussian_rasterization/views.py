@@ -19,7 +19,7 @@ import torch
 from . import _abi
 from . import _f32c, _make_inputs, _ptr, _run_forward, _state
 
-__all__ = ["ViewState", "forward_view", "backward_view", "GRAD_KEYS"]
+__all__ = ["ViewState", "forward_view", "backward_view", "ViewPipeline", "GRAD_KEYS"]
 
 # gradient buffers backward_view() accepts, named after GaussianRasterizer.forward's arguments
 GRAD_KEYS = ("means3D", "means2D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp")
@@ -114,3 +114,183 @@ def backward_view(state: ViewState, dL_dimage: torch.Tensor, grads: Dict[str, Op
             _ptr(g_sh), _ptr(g_sc), _ptr(g_rot), C.c_void_p(stream.cuda_stream)), "backward_accumulate")
         if rs.debug:
             stream.synchronize()
+
+
+class _PipeSlot:
+    def __init__(self, dev):
+        self.dev = dev
+        self.geom = self.image = self.radii = None
+        self.point_list = torch.empty(0, dtype=torch.int32, device=dev)
+        self.count_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.count_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self.ev_geom, self.ev_bin, self.ev_done = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+        self.busy = False     # a backward on the render stream may still be reading the slot
+        self.keep = None      # camera / input tensors referenced by kernels in flight
+        self.inp = None
+        self.L = 0
+        self.sig = None
+
+
+class ViewPipeline:
+    """Multi-camera forward+backward with the memory- and latency-bound half of the NEXT camera (preprocess, depth
+    order, scan, duplicate, tile sort, tile ranges) running on a high-priority stream underneath the issue-bound
+    blending kernels of the CURRENT camera (new; the reference runs everything on the legacy default stream).
+
+    Per camera k:   G stream:  geometry(k) -> [host reads L] -> binning(k)
+                    R stream (the caller's current stream):  blend_fwd(k) -> dL_fn -> backward_accumulate(k)
+    geometry(k+1) is queued before blend_fwd(k), binning(k+1) right after backward(k) has been queued.  Per-view
+    state lives in a ring of `n_slots` slots owned by the pipeline; all scratch used on G is disjoint from the
+    backward's accumulators.  Results are those of forward_view / backward_view (same kernels, same order of
+    accumulation into `grads`)."""
+
+    def __init__(self, device=None, n_slots: int = 3, overlap: bool = True):
+        if n_slots < 2:
+            raise ValueError("n_slots must be >= 2")
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.dev = dev
+        self.overlap = overlap
+        self.slots = [_PipeSlot(dev) for _ in range(n_slots)]
+        self.G = torch.cuda.Stream(dev, priority=-1) if overlap else None
+        self.scratch = torch.empty(0, dtype=torch.uint8, device=dev)
+        self.ev_start = torch.cuda.Event()
+
+    # ---- helpers ------------------------------------------------------------------------------------------
+    def _gstream(self):
+        return self.G if self.overlap else torch.cuda.current_stream(self.dev)
+
+    def _ensure(self, cur, nbytes, dtype=torch.uint8):
+        """Grow a pipeline-owned buffer; both streams are drained first because the old block goes back to the
+        caching allocator, which only orders reuse on the allocating stream."""
+        if cur is not None and cur.numel() * cur.element_size() >= nbytes:
+            return cur
+        torch.cuda.synchronize(self.dev)
+        n = int(nbytes * 1.25) + 256
+        return torch.empty(n // torch.empty(0, dtype=dtype).element_size() + 1, dtype=dtype, device=self.dev)
+
+    def _geometry(self, slot, rs, t, P, M):
+        lib = _abi.lib()
+        W, H = int(rs.image_width), int(rs.image_height)
+        G = self._gstream()
+        if slot.busy and self.overlap:
+            G.wait_event(slot.ev_done)
+        sig = (P, W, H)
+        if slot.sig != sig:
+            slot.geom = self._ensure(None, lib.gsr_geom_bytes(P))
+            slot.image = self._ensure(None, lib.gsr_image_bytes(W, H))
+            slot.radii = torch.empty((P,), dtype=torch.int32, device=self.dev)
+            slot.sig = sig
+        self.scratch = self._ensure(self.scratch, lib.gsr_scratch_bytes(P, max(slot.point_list.numel(), 1), W, H))
+        keep = []
+        inp = _make_inputs(rs, P, M, 0, t["means3D"], t["shs"], t["colors_precomp"], t["opacities"], t["scales"],
+                           t["rotations"], t["cov3D_precomp"], None, keep)
+        slot.keep, slot.inp = keep, inp
+        _abi.check(lib.gsr_forward_geometry(C.byref(inp), _ptr(slot.geom), _ptr(slot.radii), _ptr(self.scratch),
+                                            self.scratch.numel(), _ptr(slot.count_dev),
+                                            C.c_void_p(slot.count_host.data_ptr()), C.c_void_p(G.cuda_stream)),
+                   "forward_geometry")
+        slot.ev_geom.record(G)
+
+    def _binning(self, slot, rs, P):
+        lib = _abi.lib()
+        W, H = int(rs.image_width), int(rs.image_height)
+        G = self._gstream()
+        slot.ev_geom.synchronize()  # the one host sync per view (reference: rasterizer_impl.cu:281)
+        L = slot.L = int(slot.count_host.item()) & 0xFFFFFFFF
+        if slot.point_list.numel() < max(L, 1):
+            slot.point_list = self._ensure(slot.point_list, 4 * max(L, 1), torch.int32)
+        self.scratch = self._ensure(self.scratch, lib.gsr_scratch_bytes(P, L, W, H))
+        _abi.check(lib.gsr_forward_binning(C.byref(slot.inp), _ptr(slot.geom), _ptr(slot.radii), L, _ptr(slot.point_list),
+                                           _ptr(slot.image), _ptr(self.scratch), self.scratch.numel(),
+                                           C.c_void_p(G.cuda_stream)), "forward_binning")
+        slot.ev_bin.record(G)
+
+    def _blend(self, slot, rs):
+        lib = _abi.lib()
+        R = torch.cuda.current_stream(self.dev)
+        if self.overlap:
+            R.wait_event(slot.ev_bin)
+        color = torch.empty((3, int(rs.image_height), int(rs.image_width)), dtype=torch.float32, device=self.dev)
+        _abi.check(lib.gsr_forward_blend(C.byref(slot.inp), _ptr(slot.geom), _ptr(slot.point_list), _ptr(slot.image),
+                                         _ptr(color), None, C.c_void_p(R.cuda_stream)), "forward_blend")
+        return color
+
+    def _backward(self, slot, rs, t, P, M, dL_dimage, grads):
+        lib = _abi.lib()
+        R = torch.cuda.current_stream(self.dev)
+        H, W = int(rs.image_height), int(rs.image_width)
+        dpix = _f32c(dL_dimage, "dL_dimage")
+        if dpix is None or dpix.numel() != 3 * H * W:
+            raise RuntimeError(f"dL_dimage must have 3*{H}*{W} elements")
+        g = lambda n: _ptr(grads.get(n))
+        _abi.check(lib.gsr_backward_accumulate(
+            C.byref(slot.inp), _ptr(slot.geom), _ptr(slot.radii), slot.L, _ptr(slot.point_list), _ptr(slot.image),
+            _ptr(self.scratch), self.scratch.numel(), _ptr(dpix), g("means2D"), g("opacities"), g("colors_precomp"),
+            g("means3D"), g("cov3D_precomp"), g("shs"), g("scales"), g("rotations"), C.c_void_p(R.cuda_stream)),
+            "backward_accumulate")
+        slot.ev_done.record(R)
+        slot.busy = True
+
+    # ---- public -------------------------------------------------------------------------------------------
+    def step(self, settings, dL_fn, grads, means3D, opacities, shs=None, colors_precomp=None, scales=None,
+             rotations=None, cov3D_precomp=None):
+        """Render every camera in `settings` (GaussianRasterizationSettings) and ADD its gradients to `grads` (as
+        backward_view does).  `dL_fn(image, k)` receives the plain (3,H,W) render of camera k on the current stream
+        and returns dL/dimage -- or None to skip that camera's backward (forward-only use).  Returns the list of
+        duplicate counts (num_rendered) per camera."""
+        if (shs is None) == (colors_precomp is None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        if means3D.ndimension() != 2 or means3D.size(1) != 3:
+            raise RuntimeError("means3D must have dimensions (num_points, 3)")
+        if not means3D.is_cuda:
+            raise RuntimeError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+        for k in grads:
+            if k not in GRAD_KEYS:
+                raise Exception(f"unknown gradient buffer '{k}' (expected one of {GRAD_KEYS})")
+        P, n = means3D.size(0), len(settings)
+        counts = []
+        if P == 0 or n == 0:
+            return counts
+        with torch.no_grad(), torch.cuda.device(self.dev):
+            t = dict(means3D=_f32c(means3D, "means3D"), shs=_f32c(shs, "shs"),
+                     colors_precomp=_f32c(colors_precomp, "colors_precomp"), opacities=_f32c(opacities, "opacities"),
+                     scales=_f32c(scales, "scales"), rotations=_f32c(rotations, "rotations"),
+                     cov3D_precomp=_f32c(cov3D_precomp, "cov3D_precomp"))
+            M = t["shs"].size(1) if t["shs"] is not None else 0
+            for name in ("means3D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp"):
+                need = t[name] is not None
+                gbuf = grads.get(name)
+                if gbuf is None and need and any(grads.get(x) is not None for x in grads):
+                    raise Exception(f"grads['{name}'] is required for the inputs these views are rendered with")
+                if gbuf is not None and (not gbuf.is_cuda or gbuf.dtype != torch.float32 or not gbuf.is_contiguous()
+                                         or (need and gbuf.numel() != t[name].numel())):
+                    raise RuntimeError(f"grads['{name}'] must be a contiguous float32 CUDA tensor shaped like the input")
+            R = torch.cuda.current_stream(self.dev)
+            if self.overlap:  # whatever produced the inputs on the caller's stream must be visible to G
+                self.ev_start.record(R)
+                self.G.wait_event(self.ev_start)
+            ns = len(self.slots)
+            self._geometry(self.slots[0], settings[0], t, P, M)
+            self._binning(self.slots[0], settings[0], P)
+            for k in range(n):
+                slot = self.slots[k % ns]
+                if k + 1 < n:
+                    self._geometry(self.slots[(k + 1) % ns], settings[k + 1], t, P, M)
+                color = self._blend(slot, settings[k])
+                counts.append(slot.L)
+                with torch.enable_grad():
+                    dL = dL_fn(color, k)
+                if dL is not None:
+                    self._backward(slot, settings[k], t, P, M, dL, grads)
+                else:
+                    slot.ev_done.record(R)
+                    slot.busy = True
+                if k + 1 < n:
+                    self._binning(self.slots[(k + 1) % ns], settings[k + 1], P)
+            if self.overlap:  # later work on the caller's stream (and frees of the inputs) must follow G's reads
+                ev = torch.cuda.Event()
+                ev.record(self.G)
+                R.wait_event(ev)
+        return counts

@@ -6,9 +6,11 @@ config C3's 64 views / 8 GPUs) are rendered forward and backward against a repli
 set (config C2: 1M Gaussians, SH degree 3, 1920x1080), attribute gradients accumulate over the
 views and -- for N > 1 -- are summed with one NCCL all-reduce.  views/sec = N * views * K / t.
 
-  value     inputs resident in HBM, public Python API: views.forward_view + views.backward_view (each view's
-            gradients are added straight into the flat all-reduce bucket); `--api autograd` times the
-            drop-in GaussianRasterizer + autograd backward instead
+  value     inputs resident in HBM, public Python API: views.ViewPipeline.step (each view's gradients are added
+            straight into the flat all-reduce bucket; preprocess / sorts / binning of the next camera run on a
+            high-priority stream underneath the blending kernels of the current one).  `--no-overlap` keeps one
+            stream (views.forward_view + backward_view); `--api autograd` times the drop-in GaussianRasterizer +
+            autograd backward instead.  The `stages` table is always measured on one stream.
   e2e       same step driven from HOST buffers through pipeline.HostStepPipeline: Gaussian attributes,
             camera matrices and dL/dpixel copied from pinned host memory every step, gradients read back
             to the host every step; copies of neighbouring steps overlap compute (depth-2 pipeline, three
@@ -48,6 +50,8 @@ def parse_args():
     ap.add_argument("--P", type=int, default=None, help="override Gaussian count (debug)")
     ap.add_argument("--api", default="views", choices=["views", "autograd"],
                     help="views: forward_view/backward_view accumulate API; autograd: drop-in GaussianRasterizer")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="views API without the two-stream ViewPipeline (everything on one stream)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-views", type=int, default=1)
@@ -217,6 +221,9 @@ class Workload:
         self.bg = torch.zeros(3, device=dev)
         self.api = args.api
         self.grads = {n: self.bucket.grad(n) for n, _ in ATTRS}
+        self.overlap = not args.no_overlap
+        self.vp = None
+        self.settings_list = None
         self.host_grad2 = torch.empty_like(self.host_param).pin_memory()
         self.pipe = None
         self.h2d_bytes = self.host_param.numel() * 4 + self.host_dL.numel() * 4 + self.host_cam.numel() * 4
@@ -252,10 +259,20 @@ class Workload:
             scales=p["scales"], rotations=p["rotations"])
         self.last_fn, self.last_radii, self.last_color = color.grad_fn, radii, color
 
-    def step(self, dist=None):
+    def step(self, dist=None, overlap=None):
         self.flat_grad.zero_()
-        for v in range(len(self.cams)):
-            self.view_fwd_bwd(v)
+        overlap = self.overlap if overlap is None else overlap
+        if self.api == "views" and overlap:
+            from diff_gaussian_rasterization import views
+            if self.vp is None:
+                self.vp = views.ViewPipeline(self.dev)
+                self.settings_list = [self.settings(v) for v in range(len(self.cams))]
+            p = self.params
+            self.vp.step(self.settings_list, lambda img, k: self.dev_dL[k], self.grads, p["means3D"], p["opacities"],
+                         shs=p["shs"], scales=p["scales"], rotations=p["rotations"])
+        else:
+            for v in range(len(self.cams)):
+                self.view_fwd_bwd(v)
         if dist is not None:
             dist.all_reduce(self.flat_grad)
 
@@ -345,7 +362,7 @@ def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
     lib = _abi.lib()
     lib.gsr_profile_enable(1)
     for _ in range(steps):
-        wl.step(None)
+        wl.step(None, overlap=False)  # per-kernel durations: one stream, nothing running underneath
     ms = (C.c_float * len(_abi.STAGES))()
     calls = (C.c_int32 * len(_abi.STAGES))()
     lib.gsr_profile_read(ms, calls)

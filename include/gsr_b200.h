@@ -91,6 +91,16 @@ int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* ra
                        uint32_t* point_list, void* image, void* scratch, size_t scratch_bytes,
                        float* out_color, float* out_objects, void* stream);
 
+/* ---- phase 2 in two calls, so that a driver can put them on different streams: binning (duplicateWithKeys + sort +
+ *      identifyTileRanges; uses `scratch`, writes point_list and the tile ranges inside `image`) and blending
+ *      (reads geom / point_list / image only).  gsr_forward_render == gsr_forward_binning then gsr_forward_blend.
+ *      views.ViewPipeline runs geometry + binning of the next camera on a high-priority stream underneath the
+ *      blending kernels of the current one. ---- */
+int gsr_forward_binning(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, uint32_t* point_list,
+                        void* image, void* scratch, size_t scratch_bytes, void* stream);
+int gsr_forward_blend(const gsr_inputs* in, const void* geom, const uint32_t* point_list, void* image,
+                      float* out_color, float* out_objects, void* stream);
+
 /* ---- backward (Rasterizer::backward, rasterizer_impl.cu:340-433; rasterize_points.cu:117-196).
  *      All gradient outputs are fully written (no pre-zeroing by the caller).  Pass NULL for
  *      dL_dsh / dL_dscale+dL_drot / dL_dcov3D / dL_dcolor when the matching input is absent.
