@@ -225,7 +225,7 @@ static int backward_impl(const gsr_inputs* in, const void* geom, const int32_t* 
                          const uint32_t* point_list, const void* image, void* scratch, size_t scratch_bytes,
                          const float* dL_dpix, const float* dL_dobjpix, float* dL_dmean2D, float* dL_dopacity,
                          float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
-                         float* dL_drot, float* dL_dobj, bool accumulate, void* stream) {
+                         float* dL_drot, float* dL_dobj, bool accumulate, int phase, void* stream) {
   GSR_TRY(check_inputs(in));
   cudaStream_t st = (cudaStream_t)stream;
   if (in->P == 0) return GSR_OK;
@@ -241,12 +241,17 @@ static int backward_impl(const gsr_inputs* in, const void* geom, const int32_t* 
   Geom g(const_cast<void*>(geom), in->P);
   Image im(const_cast<void*>(image), in->W, in->H);
   Scratch s(scratch, in->P, 0);
-  { StageScope ps(ST_BLEND_BWD, st); GSR_TRY(launch_blend_bwd(*in, g, im, point_list, dL_dpix, dL_dobjpix, s.accum, dL_dobj, st)); }
+  if (phase & 1) {
+    StageScope ps(ST_BLEND_BWD, st);
+    GSR_TRY(launch_blend_bwd(*in, g, im, point_list, dL_dpix, dL_dobjpix, s.accum, dL_dobj, st));
+  }
   GSR_TRY(debug_sync(in, st, "blend_bwd"));
-  { StageScope ps(ST_PREPROCESS_BWD, st);
+  if (phase & 2) {
+    StageScope ps(ST_PREPROCESS_BWD, st);
     GSR_TRY(launch_preprocess_bwd(*in, g, radii, s.accum, dL_dmean2D, dL_dopacity, in->colors_precomp ? dL_dcolor : nullptr,
                                   dL_dmean3D, in->cov3D_precomp ? dL_dcov3D : nullptr, in->shs ? dL_dsh : nullptr,
-                                  in->scales ? dL_dscale : nullptr, in->scales ? dL_drot : nullptr, accumulate, st)); }
+                                  in->scales ? dL_dscale : nullptr, in->scales ? dL_drot : nullptr, accumulate, st));
+  }
   GSR_TRY(debug_sync(in, st, "preprocess_bwd"));
   return GSR_OK;
 }
@@ -256,7 +261,7 @@ int gsr_backward(const gsr_inputs* in, const void* geom, const int32_t* radii, i
                  float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
                  float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dobj, void* stream) {
   return backward_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, dL_dpix, dL_dobjpix, dL_dmean2D,
-                       dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dobj, false, stream);
+                       dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dobj, false, 3, stream);
 }
 
 int gsr_backward_accumulate(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
@@ -265,7 +270,17 @@ int gsr_backward_accumulate(const gsr_inputs* in, const void* geom, const int32_
                             float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                             void* stream) {
   return backward_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, dL_dpix, nullptr, dL_dmean2D,
-                       dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, true, stream);
+                       dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, true, 3, stream);
+}
+
+int gsr_backward_accumulate_phase(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
+                                  const uint32_t* point_list, const void* image, void* scratch, size_t scratch_bytes,
+                                  const float* dL_dpix, float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor,
+                                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                  int32_t phase, void* stream) {
+  if (phase < 1 || phase > 3) { set_error("backward_accumulate_phase: phase must be 1, 2 or 3"); return GSR_ERR_INVALID; }
+  return backward_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, dL_dpix, nullptr, dL_dmean2D,
+                       dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, true, phase, stream);
 }
 
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* /*projmatrix*/,

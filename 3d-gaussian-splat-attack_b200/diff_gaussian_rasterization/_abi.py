@@ -54,6 +54,9 @@ EXPORTS = {
                                     C.c_void_p, C.c_void_p]),
     "gsr_image_to_u8_hwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "gsr_detector_scale": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "gsr_backward_accumulate_phase": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                                C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p] + [C.c_void_p] * 8 +
+                                      [C.c_int32, C.c_void_p]),
     "gsr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_sort_pairs_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),

@@ -137,7 +137,8 @@ class ViewPipeline:
     blending kernels of the CURRENT camera (new; the reference runs everything on the legacy default stream).
 
     Per camera k:   G stream:  geometry(k) -> [host reads L] -> binning(k)
-                    R stream (the caller's current stream):  blend_fwd(k) -> dL_fn -> backward_accumulate(k)
+                    R stream (the caller's current stream):  blend_fwd(k) -> dL_fn -> blend_bwd(k)
+                    B stream:  preprocess_bwd(k), adding into `grads` (HBM-bound, under blend_fwd(k+1))
     geometry(k+1) is queued before blend_fwd(k), binning(k+1) right after backward(k) has been queued.  Per-view
     state lives in a ring of `n_slots` slots owned by the pipeline; all scratch used on G is disjoint from the
     backward's accumulators.  Results are those of forward_view / backward_view (same kernels, same order of
@@ -151,8 +152,10 @@ class ViewPipeline:
         self.overlap = overlap
         self.slots = [_PipeSlot(dev) for _ in range(n_slots)]
         self.G = torch.cuda.Stream(dev, priority=-1) if overlap else None
+        self.B = torch.cuda.Stream(dev, priority=-1) if overlap else None
         self.scratch = torch.empty(0, dtype=torch.uint8, device=dev)
-        self.ev_start = torch.cuda.Event()
+        self.ev_start, self.ev_bb, self.ev_pb = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+        self.pb_pending = False
 
     # ---- helpers ------------------------------------------------------------------------------------------
     def _gstream(self):
@@ -222,12 +225,29 @@ class ViewPipeline:
         if dpix is None or dpix.numel() != 3 * H * W:
             raise RuntimeError(f"dL_dimage must have 3*{H}*{W} elements")
         g = lambda n: _ptr(grads.get(n))
-        _abi.check(lib.gsr_backward_accumulate(
-            C.byref(slot.inp), _ptr(slot.geom), _ptr(slot.radii), slot.L, _ptr(slot.point_list), _ptr(slot.image),
-            _ptr(self.scratch), self.scratch.numel(), _ptr(dpix), g("means2D"), g("opacities"), g("colors_precomp"),
-            g("means3D"), g("cov3D_precomp"), g("shs"), g("scales"), g("rotations"), C.c_void_p(R.cuda_stream)),
-            "backward_accumulate")
-        slot.ev_done.record(R)
+
+        def phase(ph, stream):
+            _abi.check(lib.gsr_backward_accumulate_phase(
+                C.byref(slot.inp), _ptr(slot.geom), _ptr(slot.radii), slot.L, _ptr(slot.point_list), _ptr(slot.image),
+                _ptr(self.scratch), self.scratch.numel(), _ptr(dpix), g("means2D"), g("opacities"), g("colors_precomp"),
+                g("means3D"), g("cov3D_precomp"), g("shs"), g("scales"), g("rotations"), ph,
+                C.c_void_p(stream.cuda_stream)), "backward_accumulate")
+
+        if not self.overlap:
+            phase(3, R)
+            slot.ev_done.record(R)
+        else:
+            # the issue-bound per-tile half stays on R; the HBM-bound per-Gaussian half goes to stream B, where it
+            # runs underneath the next camera's blend_fwd.  The accumulators are shared: the next blend_bwd waits.
+            if self.pb_pending:
+                R.wait_event(self.ev_pb)
+            phase(1, R)
+            self.ev_bb.record(R)
+            self.B.wait_event(self.ev_bb)
+            phase(2, self.B)
+            self.ev_pb.record(self.B)
+            slot.ev_done.record(self.B)
+            self.pb_pending = True
         slot.busy = True
 
     # ---- public -------------------------------------------------------------------------------------------
@@ -289,8 +309,11 @@ class ViewPipeline:
                     slot.busy = True
                 if k + 1 < n:
                     self._binning(self.slots[(k + 1) % ns], settings[k + 1], P)
-            if self.overlap:  # later work on the caller's stream (and frees of the inputs) must follow G's reads
+            if self.overlap:  # later work on the caller's stream (and frees of the inputs) must follow G's and B's
                 ev = torch.cuda.Event()
                 ev.record(self.G)
                 R.wait_event(ev)
+                if self.pb_pending:
+                    R.wait_event(self.ev_pb)
+                    self.pb_pending = False
         return counts

@@ -124,6 +124,16 @@ int gsr_backward_accumulate(const gsr_inputs* in, const void* geom, const int32_
                             float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
                             float* dL_drot, void* stream);
 
+/* Same, one half at a time so a driver can put the halves on different streams: phase 1 = the per-tile blending
+ * gradients into the scratch accumulators (issue-bound), phase 2 = the per-Gaussian backward that adds into the
+ * caller's buffers (HBM-bound), phase 3 = both.  Phase 2 of a view must follow its phase 1, and the next view's
+ * phase 1 must follow this view's phase 2 (they share the accumulators in `scratch`). */
+int gsr_backward_accumulate_phase(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
+                                  const uint32_t* point_list, const void* image, void* scratch, size_t scratch_bytes,
+                                  const float* dL_dpix, float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor,
+                                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                  int32_t phase, void* stream);
+
 /* ---- markVisible (rasterizer_impl.cu:141-153, checkFrustum :54-66); present is (P) bytes ---- */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);
