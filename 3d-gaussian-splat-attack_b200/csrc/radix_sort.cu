@@ -12,6 +12,7 @@
 //      decoupled look-back over per-digit status words, stages the tile in shared memory in
 //      sorted order and writes it out in coalesced per-digit runs.
 // HBM traffic: 8 B/pair (histogram) + 24 B/pair/pass.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace gsr {
@@ -92,11 +93,18 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
   extern __shared__ __align__(16) unsigned char smem_raw[];
   PassSmem<KeyT>& S = *reinterpret_cast<PassSmem<KeyT>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t ntiles = (uint32_t)((n + SORT_TILE - 1) / SORT_TILE);
+  // a block keeps taking tiles (tickets are handed out in order, so look-back cannot deadlock) until none is left;
+  // launched with one block per tile this loop runs once, launched with fewer it is a persistent kernel with a
+  // bounded footprint per SM (views.ViewPipeline runs the sorts underneath the blending kernels)
+  for (;;) {
+  __syncthreads();
   if (tid == 0) S.tile = atomicAdd(ticket, 1u);
 #pragma unroll
   for (int w = 0; w < NWARPS; w++) S.warp_hist[w][tid] = 0;
   __syncthreads();
   const uint32_t tile = S.tile;
+  if (tile >= ntiles) break;
   const int64_t tile_base = (int64_t)tile * SORT_TILE;
   const int tile_n = (int)min((int64_t)SORT_TILE, n - tile_base);
 
@@ -198,6 +206,13 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     keys_out[dst] = k;
     vals_out[dst] = S.vals[s];
   }
+  }  // next tile
+}
+
+int sort_max_blocks() {  // GSR_SORT_MAX_BLOCKS=n caps the grid of a sort pass (0 / unset: one block per tile)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("GSR_SORT_MAX_BLOCKS"); v = e ? atoi(e) : 0; if (v < 0) v = 0; }
+  return v;
 }
 
 }  // namespace
@@ -225,6 +240,8 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
   GSR_LAUNCH_CHECK("sort_scan_hist_kernel");
   const int64_t tiles = sort_tiles(n);
   const bool big = n >= SORT_SMALL_LIMIT;
+  const int cap = sort_max_blocks();
+  const unsigned grid = (unsigned)(cap > 0 && tiles > cap ? cap : tiles);
   if (big) GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT, unsigned long long>,
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PassSmem<KeyT>)));
   else GSR_CUDA_CHECK(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT, uint32_t>,
@@ -237,10 +254,10 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
     uint32_t* vout = (p & 1) ? vals0 : vals1;
     char* stp = (char*)T.status + (size_t)p * T.pass_stride;
     if (big)
-      onesweep_pass_kernel<KeyT, unsigned long long><<<(unsigned)tiles, SORT_THREADS, sizeof(PassSmem<KeyT>), st>>>(
+      onesweep_pass_kernel<KeyT, unsigned long long><<<grid, SORT_THREADS, sizeof(PassSmem<KeyT>), st>>>(
           kin, kout, vin, vout, n, shift, (1u << nb) - 1, T.hist + p * 256, (unsigned long long*)stp, T.tickets + p);
     else
-      onesweep_pass_kernel<KeyT, uint32_t><<<(unsigned)tiles, SORT_THREADS, sizeof(PassSmem<KeyT>), st>>>(
+      onesweep_pass_kernel<KeyT, uint32_t><<<grid, SORT_THREADS, sizeof(PassSmem<KeyT>), st>>>(
           kin, kout, vin, vout, n, shift, (1u << nb) - 1, T.hist + p * 256, (uint32_t*)stp, T.tickets + p);
     GSR_LAUNCH_CHECK("onesweep_pass_kernel");
   }
