@@ -20,10 +20,33 @@ import torch
 from . import GaussianRasterizationSettings
 from . import views as _views
 
-__all__ = ["HostStepPipeline", "ATTRS"]
+__all__ = ["HostStepPipeline", "ATTRS", "bind_host_to_gpu_numa"]
 
 # flat layout: name -> floats per Gaussian (SH width is 3*M, filled in per instance)
 ATTRS = ("means3D", "shs", "scales", "rotations", "opacities")
+
+
+def bind_host_to_gpu_numa(device) -> Optional[str]:
+    """Pin the calling process to the CPUs of the NUMA node the GPU hangs off (sysfs local_cpulist of its PCI
+    function), so that pinned host buffers allocated afterwards are local to that GPU's PCIe root.  With one
+    process per GPU this keeps the host<->device copies of 8 ranks off the inter-socket link.  Returns the cpu
+    list used, or None when the topology cannot be read (nothing is changed then)."""
+    import os
+    try:
+        pr = torch.cuda.get_device_properties(torch.device(device))
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        cpulist = open(f"/sys/bus/pci/devices/{bdf}/local_cpulist").read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0) if cpus & os.sched_getaffinity(0) else cpus
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpulist
+    except Exception:
+        return None
 
 
 class _Slot:

@@ -466,6 +466,8 @@ def run_gsr(args):
         dist.init_process_group("nccl", device_id=dev)
     from diff_gaussian_rasterization import _abi
     lib = _abi.lib()  # fails loudly if the CUDA library is missing
+    from diff_gaussian_rasterization.pipeline import bind_host_to_gpu_numa
+    numa_cpus = bind_host_to_gpu_numa(dev)  # pinned host buffers below are then local to this GPU's PCIe root
     wl = Workload(args, torch, rank, world, dev)
     hbm_peak, peak_src, sm_max = load_peaks()
 
@@ -493,6 +495,7 @@ def run_gsr(args):
                "d2h_bytes_per_step": int(wl.pipe.d2h_bytes), "ms_per_step": ms_e / args.steps,
                "how": "pipeline.HostStepPipeline depth 2: H2D of step i+1 and D2H of step i-1 overlap the compute of "
                       "step i; all copies, the pipeline fill and the drain are inside the timed region",
+               "host_cpus": numa_cpus,
                "serial": {"value": world * len(wl.cams) / (ms_s * 1e-3), "unit": UNIT, "ms_per_step": ms_s,
                           "how": "same step, copies and compute on one stream, nothing overlapped"}}
 
