@@ -171,3 +171,25 @@ def test_radix_sort_ignores_bits_above_end_bit():
     ko, vo = _sort(keys, vals, 40)
     order = np.argsort(keys & np.uint64((1 << 40) - 1), kind="stable")
     assert np.array_equal(ko, keys[order]) and np.array_equal(vo, vals[order])
+
+
+@pytest.mark.parametrize("name,bwd", [("C3", True), ("C4", False)])
+def test_full_size_C3_C4_against_live_reference(name, bwd):
+    """BASELINE configs[2] (3M Gaussians, 1080p, fwd+bwd) and configs[3] (6M, 3840x2160, forward only) at full size:
+    size-independent properties, and bit-identical image / radii / duplicate count against the reference CUDA when it
+    travelled (C5, L = 1.47e9, runs in tools/config_sweep.py -- profiles/r1_config_sweep.jsonl)."""
+    s = h.make_scene(name)
+    g = h.run_gsr(s, grad=bwd, fetch=False)
+    assert np.isfinite(g["color"]).all() and g["color"].min() >= 0.0
+    assert (g["radii"] >= 0).all() and (g["radii"] > 0).sum() > s["P"] // 4
+    if bwd:
+        for k, v in g["grads"].items():
+            assert np.isfinite(v).all(), k
+        hidden = g["radii"] == 0
+        assert not g["grads"]["sh"].reshape(s["P"], -1)[hidden].any()  # unrendered Gaussians get exact zeros
+    if h.ref_available():
+        r = h.run_ref(s, grad=bwd, fetch=False)
+        assert np.array_equal(g["radii"], r["radii"])
+        assert np.array_equal(g["color"].view(np.uint32), r["color"].view(np.uint32))
+        if bwd:
+            _check_grads(g["grads"], r["grads"], skip=["colors", "cov3D", "conic"])
