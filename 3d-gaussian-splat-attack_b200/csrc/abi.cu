@@ -58,6 +58,8 @@ static int check_inputs(const gsr_inputs* in) {
   if (in->shs && (in->M < 1 || in->D < 0 || in->D > 3 || (in->D + 1) * (in->D + 1) > in->M)) {
     set_error("SH degree %d needs %d coefficients, M=%d", in->D, (in->D + 1) * (in->D + 1), in->M); return GSR_ERR_INVALID;
   }
+  if (in->shs_rest && (!in->shs || in->M < 2)) { set_error("shs_rest needs shs (the DC block) and M >= 2"); return GSR_ERR_INVALID; }
+  if (in->raw_params != 0 && in->raw_params != 1) { set_error("raw_params must be 0 or 1"); return GSR_ERR_INVALID; }
   if (in->K != 0 && (in->K != MAX_OBJ || !in->obj_feats)) { set_error("object channels: K must be 0 or 16 with obj_feats"); return GSR_ERR_INVALID; }
   return GSR_OK;
 }
@@ -232,6 +234,7 @@ static int backward_impl(const gsr_inputs* in, const void* geom, const int32_t* 
   if (!geom || !radii || !image || !scratch || !dL_dpix || (!dL_dmean2D && !accumulate) || !dL_dopacity || !dL_dmean3D ||
       (L > 0 && !point_list)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
   if (in->shs && !dL_dsh) { set_error("dL_dsh is NULL but shs given"); return GSR_ERR_INVALID; }
+  if (in->shs_rest && !in->dL_dshs_rest) { set_error("dL_dshs_rest is NULL but shs_rest given"); return GSR_ERR_INVALID; }
   if (in->scales && (!dL_dscale || !dL_drot)) { set_error("dL_dscale/dL_drot NULL but scales given"); return GSR_ERR_INVALID; }
   if (in->cov3D_precomp && !dL_dcov3D) { set_error("dL_dcov3D NULL but cov3D_precomp given"); return GSR_ERR_INVALID; }
   if (in->colors_precomp && !dL_dcolor) { set_error("dL_dcolor NULL but colors_precomp given"); return GSR_ERR_INVALID; }

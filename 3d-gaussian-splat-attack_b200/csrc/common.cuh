@@ -172,6 +172,24 @@ struct Scratch {
   }
 };
 
+// ---- activations of the raw model parameters (gsr_inputs::raw_params; scene/gaussian_model.py:97-121), written
+// like the torch kernels they replace: sigmoid = 1 / (1 + exp(-x)), exp, F.normalize = x / max(||x||_2, 1e-12)
+#ifdef __CUDACC__
+__device__ __forceinline__ float act_sigmoid(float x) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x))); }
+__device__ __forceinline__ float4 act_normalize(float4 q, float* inv_norm_out) {
+  const float n = sqrtf(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q.x, q.x), __fmul_rn(q.y, q.y)), __fmul_rn(q.z, q.z)),
+                                  __fmul_rn(q.w, q.w)));
+  const float d = fmaxf(n, 1e-12f);
+  if (inv_norm_out) *inv_norm_out = 1.0f / d;
+  return make_float4(__fdiv_rn(q.x, d), __fdiv_rn(q.y, d), __fdiv_rn(q.z, d), __fdiv_rn(q.w, d));
+}
+// coefficient i (0 .. 3M-1, coefficient-major, channel-minor) of Gaussian idx from either SH layout
+__device__ __forceinline__ float sh_coeff(const gsr_inputs& in, size_t idx, int i) {
+  if (in.shs_rest) return i < 3 ? __ldg(in.shs + 3 * idx + i) : __ldg(in.shs_rest + (size_t)(in.M - 1) * 3 * idx + (i - 3));
+  return __ldg(in.shs + (size_t)in.M * 3 * idx + i);
+}
+#endif
+
 // ---- stage launchers (each returns a gsr_status) ---------------------------------------------
 int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch& s, uint32_t* num_rendered_dev,
                           cudaStream_t st);

@@ -67,7 +67,8 @@ __device__ __forceinline__ void red_add4(float4* p, float4 v) {
 // ACC = true : the gradients of this view are ADDED to the caller's buffers (a multi-view step accumulates
 //              into one flat bucket without per-view temporaries); rows of unrendered Gaussians are untouched,
 //              dL_dmean2D may be NULL.
-template <bool ACC>
+// SPLIT / RAW: the N3 extensions (gsr_inputs::shs_rest, ::raw_params) are compiled out of the standard kernels
+template <bool ACC, bool SPLIT, bool RAW>
 __global__ void __launch_bounds__(256)
 preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, const float* __restrict__ accum,
                       float* __restrict__ dL_dmean2D, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor,
@@ -87,11 +88,17 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
   // the SH row is the largest read of this kernel: start it first
   float shv[48];
   if (live && in.shs && M == 16) {
-    const float4* sp0 = reinterpret_cast<const float4*>(in.shs) + (size_t)idx * 12;
+    if (SPLIT) {  // DC / rest blocks where the model keeps them (4-byte aligned rows)
+      const int ncoef = 3 * (in.D + 1) * (in.D + 1);
 #pragma unroll
-    for (int k = 0; k < 12; k++) {
-      const float4 t = __ldg(sp0 + k);
-      shv[4 * k] = t.x; shv[4 * k + 1] = t.y; shv[4 * k + 2] = t.z; shv[4 * k + 3] = t.w;
+      for (int k = 0; k < 48; k++) shv[k] = k < ncoef ? sh_coeff(in, (size_t)idx, k) : 0.f;
+    } else {
+      const float4* sp0 = reinterpret_cast<const float4*>(in.shs) + (size_t)idx * 12;
+#pragma unroll
+      for (int k = 0; k < 12; k++) {
+        const float4 t = __ldg(sp0 + k);
+        shv[4 * k] = t.x; shv[4 * k + 1] = t.y; shv[4 * k + 2] = t.z; shv[4 * k + 3] = t.w;
+      }
     }
   }
 #endif
@@ -109,6 +116,7 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
     a0.w = op * (0.5f * in.W) * (-co.x * m1 - co.y * m2);
     a1.x = op * (0.5f * in.H) * (-co.z * m2 - co.y * m1);
     a1.y *= -0.5f * op; a1.z *= -0.5f * op; a1.w *= -0.5f * op;
+    if (RAW) a8 *= op * (1.f - op);  // through the sigmoid: d op / d raw
   }
   if (ACC) {
     if (dL_dmean2D) { atomicAdd(dL_dmean2D + 3 * (size_t)idx, a0.w); atomicAdd(dL_dmean2D + 3 * (size_t)idx + 1, a1.x); }
@@ -210,6 +218,19 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
         for (int k = 0; k < 48; k++) outv[k] = 0.f;
         ddir = sh_backward(in.D, x, y, z, dRGB, [&](int i) { return V3{shv[3 * i], shv[3 * i + 1], shv[3 * i + 2]}; },
                            [&](int i, float w) { outv[3 * i] = w * dRGB.x; outv[3 * i + 1] = w * dRGB.y; outv[3 * i + 2] = w * dRGB.z; });
+        if (SPLIT) {
+          const int nc = (in.D + 1) * (in.D + 1);
+#pragma unroll
+          for (int k = 0; k < 16; k++) {
+            if (ACC && k >= nc) continue;  // ACC: only the active coefficients change
+            float* q3 = k == 0 ? dL_dsh + 3 * (size_t)idx : in.dL_dshs_rest + ((size_t)15 * idx + (k - 1)) * 3;
+#pragma unroll
+            for (int c2 = 0; c2 < 3; c2++) {
+              if (ACC) atomicAdd(q3 + c2, outv[3 * k + c2]);
+              else q3[c2] = outv[3 * k + c2];
+            }
+          }
+        } else {
         const int nq = ACC ? (3 * (in.D + 1) * (in.D + 1) + 3) / 4 : 12;  // ACC: only the active coefficients change
 #pragma unroll
         for (int k = 0; k < 12; k++) {
@@ -219,14 +240,23 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
             else dp[k] = o;
           }
         }
+        }
       } else {
-        const float* sp = in.shs + (size_t)idx * M * 3;
-        float* dp = dL_dsh + (size_t)idx * M * 3;
-        if (!ACC) for (int k = 0; k < 3 * M; k++) dp[k] = 0.f;
-        ddir = sh_backward(in.D, x, y, z, dRGB, [&](int i) { return V3{sp[3 * i], sp[3 * i + 1], sp[3 * i + 2]}; },
+        auto coef = [&](int i) -> float* {  // where the 3 channels of coefficient i go, in either SH layout
+          if (SPLIT) return i == 0 ? dL_dsh + 3 * (size_t)idx : in.dL_dshs_rest + ((size_t)(M - 1) * idx + (i - 1)) * 3;
+          return dL_dsh + ((size_t)M * idx + i) * 3;
+        };
+        if (!ACC) for (int i = 0; i < M; i++) { float* q3 = coef(i); q3[0] = 0.f; q3[1] = 0.f; q3[2] = 0.f; }
+        ddir = sh_backward(in.D, x, y, z, dRGB,
+                           [&](int i) {
+                             if (SPLIT) return V3{sh_coeff(in, (size_t)idx, 3 * i), sh_coeff(in, (size_t)idx, 3 * i + 1), sh_coeff(in, (size_t)idx, 3 * i + 2)};
+                             const float* sp = in.shs + (size_t)idx * M * 3;
+                             return V3{sp[3 * i], sp[3 * i + 1], sp[3 * i + 2]};
+                           },
                            [&](int i, float w) {
-                             if (ACC) { atomicAdd(dp + 3 * i, w * dRGB.x); atomicAdd(dp + 3 * i + 1, w * dRGB.y); atomicAdd(dp + 3 * i + 2, w * dRGB.z); }
-                             else { dp[3 * i] = w * dRGB.x; dp[3 * i + 1] = w * dRGB.y; dp[3 * i + 2] = w * dRGB.z; }
+                             float* q3 = coef(i);
+                             if (ACC) { atomicAdd(q3, w * dRGB.x); atomicAdd(q3 + 1, w * dRGB.y); atomicAdd(q3 + 2, w * dRGB.z); }
+                             else { q3[0] = w * dRGB.x; q3[1] = w * dRGB.y; q3[2] = w * dRGB.z; }
                            });
       }
       // d(normalised direction)/d(mean)
@@ -237,10 +267,15 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
     }
     // ---- 3D covariance -> scale / rotation ----
     if (in.scales) {
-      const float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
+      float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
+      float sa[3] = {in.scales[3 * (size_t)idx], in.scales[3 * (size_t)idx + 1], in.scales[3 * (size_t)idx + 2]};
+      float inv_qn = 1.f;
+      if (RAW) {  // same activations as the forward (scene/gaussian_model.py:97-105)
+        sa[0] = expf(sa[0]); sa[1] = expf(sa[1]); sa[2] = expf(sa[2]);
+        q = act_normalize(q, &inv_qn);
+      }
       const float r = q.x, x = q.y, y = q.z, z = q.w;
-      const float s[3] = {in.scale_modifier * in.scales[3 * (size_t)idx], in.scale_modifier * in.scales[3 * (size_t)idx + 1],
-                          in.scale_modifier * in.scales[3 * (size_t)idx + 2]};
+      const float s[3] = {in.scale_modifier * sa[0], in.scale_modifier * sa[1], in.scale_modifier * sa[2]};
       // R[c][k]: column c, row k
       const float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
                              {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
@@ -265,9 +300,22 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
       drot[1] = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
       drot[2] = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
       drot[3] = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
+      if (RAW) {
+        // back through exp (d s / d raw = s) and through normalize (d qhat / d q = (I - qhat qhat^T) / ||q||)
+#pragma unroll
+        for (int k = 0; k < 3; k++) dscale[k] *= sa[k];
+        const float qd = r * drot[0] + x * drot[1] + y * drot[2] + z * drot[3];
+        drot[0] = (drot[0] - r * qd) * inv_qn; drot[1] = (drot[1] - x * qd) * inv_qn;
+        drot[2] = (drot[2] - y * qd) * inv_qn; drot[3] = (drot[3] - z * qd) * inv_qn;
+      }
     }
   } else if (dL_dsh && M > 0) {
-    if (M == 16) {
+    if (SPLIT) {
+      float* d3 = dL_dsh + 3 * (size_t)idx;
+      d3[0] = 0.f; d3[1] = 0.f; d3[2] = 0.f;
+      float* dr = in.dL_dshs_rest + (size_t)(M - 1) * 3 * idx;
+      for (int k = 0; k < 3 * (M - 1); k++) dr[k] = 0.f;
+    } else if (M == 16) {
       float4* dp = reinterpret_cast<float4*>(dL_dsh) + (size_t)idx * 12;
 #pragma unroll
       for (int k = 0; k < 12; k++) dp[k] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -309,12 +357,16 @@ int launch_preprocess_bwd(const gsr_inputs& in, const Geom& g, const int32_t* ra
                           float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
                           float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, bool accumulate,
                           cudaStream_t st) {
-  if (accumulate)
-    preprocess_bwd_kernel<true><<<(in.P + 255) / 256, 256, 0, st>>>(in, g, radii, accum, dL_dmean2D, dL_dopacity, dL_dcolor,
-                                                                     dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
-  else
-    preprocess_bwd_kernel<false><<<(in.P + 255) / 256, 256, 0, st>>>(in, g, radii, accum, dL_dmean2D, dL_dopacity, dL_dcolor,
-                                                                      dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
+#define GSR_PRE_BWD(A, S, R)                                                                                      \
+  preprocess_bwd_kernel<A, S, R><<<(in.P + 255) / 256, 256, 0, st>>>(in, g, radii, accum, dL_dmean2D, dL_dopacity,      \
+                                                                      dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot)
+  const bool ext = in.shs_rest != nullptr || in.raw_params != 0;  // N3 paths: one extended kernel handles any mix
+  if (!ext) { if (accumulate) GSR_PRE_BWD(true, false, false); else GSR_PRE_BWD(false, false, false); }
+  else if (in.shs_rest) {
+    if (in.raw_params) { if (accumulate) GSR_PRE_BWD(true, true, true); else GSR_PRE_BWD(false, true, true); }
+    else { if (accumulate) GSR_PRE_BWD(true, true, false); else GSR_PRE_BWD(false, true, false); }
+  } else { if (accumulate) GSR_PRE_BWD(true, false, true); else GSR_PRE_BWD(false, false, true); }
+#undef GSR_PRE_BWD
   GSR_LAUNCH_CHECK("preprocess_bwd_kernel");
   return GSR_OK;
 }

@@ -199,8 +199,12 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
 #pragma unroll
         for (int k = 0; k < 6; k++) c3[k] = in.cov3D_precomp[6 * (size_t)idx + k];
       } else {
-        const float3 s = make_float3(in.scales[3 * idx], in.scales[3 * idx + 1], in.scales[3 * idx + 2]);
-        const float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
+        float3 s = make_float3(in.scales[3 * idx], in.scales[3 * idx + 1], in.scales[3 * idx + 2]);
+        float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
+        if (in.raw_params) {  // exp / normalize activations applied here (scene/gaussian_model.py:97-105)
+          s = make_float3(expf(s.x), expf(s.y), expf(s.z));
+          q = act_normalize(q, nullptr);
+        }
         covariance3d(s, in.scale_modifier, q, c3);
 #pragma unroll
         for (int k = 0; k < 6; k++) g.cov3D[6 * (size_t)idx + k] = c3[k];
@@ -231,6 +235,17 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
             rgb[0] = in.colors_precomp[3 * (size_t)idx];
             rgb[1] = in.colors_precomp[3 * (size_t)idx + 1];
             rgb[2] = in.colors_precomp[3 * (size_t)idx + 2];
+          } else if (in.shs_rest) {
+            // DC and rest blocks read where the model keeps them (no torch.cat): rows are only 4-byte aligned
+            float shv[48];
+            const int ncoef = 3 * (in.D + 1) * (in.D + 1);
+            if (in.M == 16) {
+#pragma unroll
+              for (int k = 0; k < 48; k++) shv[k] = k < ncoef ? sh_coeff(in, (size_t)idx, k) : 0.f;
+              sh_to_rgb(in.D, px, py, pz, cam.campos, [&](int i) { return shv[i]; }, rgb, cbits);
+            } else {
+              sh_to_rgb(in.D, px, py, pz, cam.campos, [&](int i) { return sh_coeff(in, (size_t)idx, i); }, rgb, cbits);
+            }
           } else if (in.M == 16) {
             // 48 floats = 12 aligned 16-byte loads
             float shv[48];
@@ -246,7 +261,7 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
             const float* sp = in.shs + (size_t)idx * in.M * 3;
             sh_to_rgb(in.D, px, py, pz, cam.campos, [&](int i) { return __ldg(sp + i); }, rgb, cbits);
           }
-          const float op = in.opacities[idx];
+          const float op = in.raw_params ? act_sigmoid(in.opacities[idx]) : in.opacities[idx];
           g.depths[idx] = depth;
           g.means2D[idx] = make_float2(pix_x, pix_y);
           g.conic_opacity[idx] = make_float4(mul(cov.z, det_inv), mul(det_inv, -cov.y), mul(cov.x, det_inv), op);

@@ -72,7 +72,8 @@ def _f32c(t, name):
     return t.contiguous()
 
 
-def _make_inputs(rs, P, M, K, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, sh_objs, keep):
+def _make_inputs(rs, P, M, K, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, sh_objs, keep,
+                 shs_rest=None, raw_params=False, dL_dshs_rest=None):
     dev = means3D.device
     bg = _f32c(rs.bg.to(dev), "bg")
     view = _f32c(rs.viewmatrix.to(dev), "viewmatrix")
@@ -89,10 +90,12 @@ def _make_inputs(rs, P, M, K, means3D, sh, colors_precomp, opacities, scales, ro
     inp.opacities, inp.scales, inp.rotations = _ptr(opacities), _ptr(scales), _ptr(rotations)
     inp.cov3D_precomp, inp.viewmatrix, inp.projmatrix = _ptr(cov3Ds_precomp), _ptr(view), _ptr(proj)
     inp.campos, inp.obj_feats = _ptr(campos), _ptr(sh_objs)
+    inp.shs_rest, inp.raw_params, inp.dL_dshs_rest = _ptr(shs_rest), int(bool(raw_params)), _ptr(dL_dshs_rest)
     return inp
 
 
-def _run_forward(rs, P, M, K, want_obj, means3D_c, sh_c, col_c, op_c, sc_c, rot_c, cov_c, obj_c):
+def _run_forward(rs, P, M, K, want_obj, means3D_c, sh_c, col_c, op_c, sc_c, rot_c, cov_c, obj_c, shs_rest=None,
+                 raw_params=False):
     """Both forward phases of one view through the C ABI (Rasterizer::forward, rasterizer_impl.cu:198-336).
     Returns (color, objects, radii, L, geom, point_list, image); the last three are what backward needs."""
     dev = means3D_c.device
@@ -109,7 +112,7 @@ def _run_forward(rs, P, M, K, want_obj, means3D_c, sh_c, col_c, op_c, sc_c, rot_
         sp = C.c_void_p(stream.cuda_stream)
         keep = []
         inp = _make_inputs(rs, P, M, K if want_obj else 0, means3D_c, sh_c, col_c, op_c, sc_c, rot_c, cov_c,
-                           obj_c, keep)
+                           obj_c, keep, shs_rest=shs_rest, raw_params=raw_params)
         if P == 0:
             color.zero_()
             if want_obj:

@@ -13,7 +13,7 @@ LIB_PATH = os.environ.get("GSR_B200_LIB") or os.path.join(_ROOT, "lib", "libgsr_
 CSRC_DIR = os.path.join(_ROOT, "csrc")
 
 GSR_OK, GSR_ERR_INVALID, GSR_ERR_CUDA, GSR_ERR_CAPACITY, GSR_ERR_PREFILTERED = 0, -1, -2, -3, -4
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class GsrInputs(C.Structure):
@@ -21,10 +21,11 @@ class GsrInputs(C.Structure):
     _fields_ = [
         ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32), ("K", C.c_int32),
         ("prefiltered", C.c_int32), ("debug", C.c_int32),
-        ("scale_modifier", C.c_float), ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("_pad", C.c_float),
+        ("scale_modifier", C.c_float), ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("raw_params", C.c_int32),
         ("bg", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p), ("colors_precomp", C.c_void_p),
         ("opacities", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
         ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p), ("obj_feats", C.c_void_p),
+        ("shs_rest", C.c_void_p), ("dL_dshs_rest", C.c_void_p),
     ]
 
 

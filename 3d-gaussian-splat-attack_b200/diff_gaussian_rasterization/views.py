@@ -22,16 +22,16 @@ from . import _f32c, _make_inputs, _ptr, _run_forward, _state
 __all__ = ["ViewState", "forward_view", "backward_view", "ViewPipeline", "GRAD_KEYS"]
 
 # gradient buffers backward_view() accepts, named after GaussianRasterizer.forward's arguments
-GRAD_KEYS = ("means3D", "means2D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp")
+GRAD_KEYS = ("means3D", "means2D", "opacities", "shs", "shs_rest", "colors_precomp", "scales", "rotations", "cov3D_precomp")
 
 
 class ViewState:
     """What one forwarded view keeps until its backward (the role of ctx.save_for_backward,
     DGR/diff_gaussian_rasterization/__init__.py:97)."""
-    __slots__ = ("rs", "P", "M", "L", "tensors", "radii", "geom", "point_list", "image")
+    __slots__ = ("rs", "P", "M", "L", "tensors", "radii", "geom", "point_list", "image", "raw_params")
 
-    def __init__(self, rs, P, M, L, tensors, radii, geom, point_list, image):
-        self.rs, self.P, self.M, self.L = rs, P, M, L
+    def __init__(self, rs, P, M, L, tensors, radii, geom, point_list, image, raw_params=False):
+        self.rs, self.P, self.M, self.L, self.raw_params = rs, P, M, L, raw_params
         self.tensors, self.radii, self.geom, self.point_list, self.image = tensors, radii, geom, point_list, image
 
     @property
@@ -40,9 +40,15 @@ class ViewState:
 
 
 def forward_view(raster_settings, means3D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
-                 cov3D_precomp=None):
+                 cov3D_precomp=None, shs_rest=None, raw_params=False):
     """Render one view.  Same argument meaning and exclusivity rules as GaussianRasterizer.forward
-    (DGR/diff_gaussian_rasterization/__init__.py:187-220).  Returns (color (3,H,W), radii (P,) int32, ViewState)."""
+    (DGR/diff_gaussian_rasterization/__init__.py:187-220).  Returns (color (3,H,W), radii (P,) int32, ViewState).
+
+    Fused model activations (render() materialises them per call, gaussian_renderer/__init__.py:53-81):
+      shs_rest     pass the model's `_features_dc` (P,1,3) as `shs` and `_features_rest` (P,M-1,3) here: no torch.cat
+      raw_params   `opacities`, `scales`, `rotations` are the RAW `_opacity`, `_scaling`, `_rotation`; sigmoid / exp /
+                   normalize (scene/gaussian_model.py:97-121) run inside the preprocess kernels and backward_view
+                   returns gradients w.r.t. the raw parameters."""
     if (shs is None) == (colors_precomp is None):
         raise Exception('Please provide excatly one of either SHs or precomputed colors!')
     if ((scales is None or rotations is None) and cov3D_precomp is None) or \
@@ -57,13 +63,27 @@ def forward_view(raster_settings, means3D, opacities, shs=None, colors_precomp=N
         m = _f32c(means3D, "means3D") if P else means3D
         t = dict(shs=_f32c(shs, "shs"), colors_precomp=_f32c(colors_precomp, "colors_precomp"),
                  opacities=_f32c(opacities, "opacities"), scales=_f32c(scales, "scales"),
-                 rotations=_f32c(rotations, "rotations"), cov3D_precomp=_f32c(cov3D_precomp, "cov3D_precomp"))
-        M = t["shs"].size(1) if t["shs"] is not None else 0
+                 rotations=_f32c(rotations, "rotations"), cov3D_precomp=_f32c(cov3D_precomp, "cov3D_precomp"),
+                 shs_rest=_f32c(shs_rest, "shs_rest"))
+        M = _sh_count(t["shs"], t["shs_rest"])
         color, _, radii, L, geom, point_list, image = _run_forward(
             raster_settings, P, M, 0, False, m, t["shs"], t["colors_precomp"], t["opacities"], t["scales"],
-            t["rotations"], t["cov3D_precomp"], None)
+            t["rotations"], t["cov3D_precomp"], None, shs_rest=t["shs_rest"], raw_params=raw_params)
     t["means3D"] = m
-    return color, radii, ViewState(raster_settings, P, M, L, t, radii, geom, point_list, image)
+    return color, radii, ViewState(raster_settings, P, M, L, t, radii, geom, point_list, image, bool(raw_params))
+
+
+def _sh_count(shs, shs_rest):
+    """Total SH coefficients M from either layout: shs (P,M,3), or shs (P,1,3) + shs_rest (P,M-1,3)."""
+    if shs is None:
+        if shs_rest is not None:
+            raise Exception("shs_rest needs shs (the DC block)")
+        return 0
+    if shs_rest is None:
+        return shs.size(1)
+    if shs.size(1) != 1:
+        raise Exception("with shs_rest, shs must be the DC block (P,1,3)")
+    return 1 + shs_rest.size(1)
 
 
 def backward_view(state: ViewState, dL_dimage: torch.Tensor, grads: Dict[str, Optional[torch.Tensor]]) -> None:
@@ -92,7 +112,9 @@ def backward_view(state: ViewState, dL_dimage: torch.Tensor, grads: Dict[str, Op
     g_m3 = buf("means3D", True, P * 3)
     g_m2 = buf("means2D", False, P * 3)
     g_op = buf("opacities", True, P)
-    g_sh = buf("shs", t["shs"] is not None, P * state.M * 3)
+    split = t.get("shs_rest") is not None
+    g_sh = buf("shs", t["shs"] is not None, P * (1 if split else state.M) * 3)
+    g_rest = buf("shs_rest", split, P * (state.M - 1) * 3)
     g_col = buf("colors_precomp", t["colors_precomp"] is not None, P * 3)
     g_sc = buf("scales", t["scales"] is not None, P * 3)
     g_rot = buf("rotations", t["rotations"] is not None, P * 4)
@@ -106,7 +128,8 @@ def backward_view(state: ViewState, dL_dimage: torch.Tensor, grads: Dict[str, Op
         stream = torch.cuda.current_stream(dev)
         keep = []
         inp = _make_inputs(rs, P, state.M, 0, t["means3D"], t["shs"], t["colors_precomp"], t["opacities"], t["scales"],
-                           t["rotations"], t["cov3D_precomp"], None, keep)
+                           t["rotations"], t["cov3D_precomp"], None, keep, shs_rest=t.get("shs_rest"),
+                           raw_params=state.raw_params, dL_dshs_rest=g_rest)
         scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, 0, W, H))
         _abi.check(lib.gsr_backward_accumulate(
             C.byref(inp), _ptr(state.geom), _ptr(state.radii), state.L, _ptr(state.point_list), _ptr(state.image),
@@ -170,7 +193,7 @@ class ViewPipeline:
         n = int(nbytes * 1.25) + 256
         return torch.empty(n // torch.empty(0, dtype=dtype).element_size() + 1, dtype=dtype, device=self.dev)
 
-    def _geometry(self, slot, rs, t, P, M):
+    def _geometry(self, slot, rs, t, P, M, grads=None, raw_params=False):
         lib = _abi.lib()
         W, H = int(rs.image_width), int(rs.image_height)
         G = self._gstream()
@@ -185,7 +208,8 @@ class ViewPipeline:
         self.scratch = self._ensure(self.scratch, lib.gsr_scratch_bytes(P, max(slot.point_list.numel(), 1), W, H))
         keep = []
         inp = _make_inputs(rs, P, M, 0, t["means3D"], t["shs"], t["colors_precomp"], t["opacities"], t["scales"],
-                           t["rotations"], t["cov3D_precomp"], None, keep)
+                           t["rotations"], t["cov3D_precomp"], None, keep, shs_rest=t.get("shs_rest"),
+                           raw_params=raw_params, dL_dshs_rest=(grads or {}).get("shs_rest"))
         slot.keep, slot.inp = keep, inp
         _abi.check(lib.gsr_forward_geometry(C.byref(inp), _ptr(slot.geom), _ptr(slot.radii), _ptr(self.scratch),
                                             self.scratch.numel(), _ptr(slot.count_dev),
@@ -252,11 +276,13 @@ class ViewPipeline:
 
     # ---- public -------------------------------------------------------------------------------------------
     def step(self, settings, dL_fn, grads, means3D, opacities, shs=None, colors_precomp=None, scales=None,
-             rotations=None, cov3D_precomp=None):
+             rotations=None, cov3D_precomp=None, shs_rest=None, raw_params=False):
         """Render every camera in `settings` (GaussianRasterizationSettings) and ADD its gradients to `grads` (as
         backward_view does).  `dL_fn(image, k)` receives the plain (3,H,W) render of camera k on the current stream
         and returns dL/dimage -- or None to skip that camera's backward (forward-only use).  Returns the list of
-        duplicate counts (num_rendered) per camera."""
+        duplicate counts (num_rendered) per camera.  `shs_rest` / `raw_params` as in forward_view (fused model
+        activations; gradients then refer to the raw parameters, `grads["shs"]` to the DC block and
+        `grads["shs_rest"]` to the rest block)."""
         if (shs is None) == (colors_precomp is None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
         if ((scales is None or rotations is None) and cov3D_precomp is None) or \
@@ -277,9 +303,9 @@ class ViewPipeline:
             t = dict(means3D=_f32c(means3D, "means3D"), shs=_f32c(shs, "shs"),
                      colors_precomp=_f32c(colors_precomp, "colors_precomp"), opacities=_f32c(opacities, "opacities"),
                      scales=_f32c(scales, "scales"), rotations=_f32c(rotations, "rotations"),
-                     cov3D_precomp=_f32c(cov3D_precomp, "cov3D_precomp"))
-            M = t["shs"].size(1) if t["shs"] is not None else 0
-            for name in ("means3D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp"):
+                     cov3D_precomp=_f32c(cov3D_precomp, "cov3D_precomp"), shs_rest=_f32c(shs_rest, "shs_rest"))
+            M = _sh_count(t["shs"], t["shs_rest"])
+            for name in ("means3D", "opacities", "shs", "shs_rest", "colors_precomp", "scales", "rotations", "cov3D_precomp"):
                 need = t[name] is not None
                 gbuf = grads.get(name)
                 if gbuf is None and need and any(grads.get(x) is not None for x in grads):
@@ -292,12 +318,12 @@ class ViewPipeline:
                 self.ev_start.record(R)
                 self.G.wait_event(self.ev_start)
             ns = len(self.slots)
-            self._geometry(self.slots[0], settings[0], t, P, M)
+            self._geometry(self.slots[0], settings[0], t, P, M, grads, raw_params)
             self._binning(self.slots[0], settings[0], P)
             for k in range(n):
                 slot = self.slots[k % ns]
                 if k + 1 < n:
-                    self._geometry(self.slots[(k + 1) % ns], settings[k + 1], t, P, M)
+                    self._geometry(self.slots[(k + 1) % ns], settings[k + 1], t, P, M, grads, raw_params)
                 color = self._blend(slot, settings[k])
                 counts.append(slot.L)
                 with torch.enable_grad():

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 1
+#define GSR_ABI_VERSION 2
 
 typedef enum {
   GSR_OK = 0,
@@ -50,7 +50,10 @@ typedef struct gsr_inputs {
   int32_t prefiltered;    /* reference flag: trap if a Gaussian is near-culled              */
   int32_t debug;          /* reference flag: synchronise + check after every stage          */
   float scale_modifier, tanfovx, tanfovy;
-  float _pad;
+  int32_t raw_params;     /* 0: inputs are what render() passes (gaussian_renderer/__init__.py:53-81).  1: `opacities`,
+                           * `scales`, `rotations` are the model's RAW parameters and the activations of
+                           * scene/gaussian_model.py:97-121 (sigmoid, exp, normalize) are applied inside preprocess;
+                           * their gradient outputs are then w.r.t. the raw parameters           */
   const float* bg;             /* (>=3)                                                     */
   const float* means3D;        /* (P,3)                                                     */
   const float* shs;            /* (P,M,3) or NULL                                           */
@@ -63,6 +66,11 @@ typedef struct gsr_inputs {
   const float* projmatrix;     /* (4,4) column-major in memory                              */
   const float* campos;         /* (3)                                                       */
   const float* obj_feats;      /* (P,K) or NULL                                             */
+  const float* shs_rest;       /* NULL, or (P,M-1,3): then `shs` is only the DC block (P,1,3) -- the model's
+                                * _features_dc / _features_rest without the per-call torch.cat of
+                                * scene/gaussian_model.py:110-113                                              */
+  float* dL_dshs_rest;         /* output of the backward calls when shs_rest is given: (P,M-1,3); dL_dsh is then
+                                * (P,1,3)                                                                      */
 } gsr_inputs;
 
 int gsr_abi_version(void);

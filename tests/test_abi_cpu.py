@@ -33,8 +33,8 @@ def test_library_exports_every_declared_symbol():
 def test_abi_version_and_struct_layout():
     from diff_gaussian_rasterization import _abi
     assert _abi.lib().gsr_abi_version() == _abi.ABI_VERSION
-    # 8 int32 + 4 float + 12 pointers
-    assert C.sizeof(_abi.GsrInputs) == 8 * 4 + 4 * 4 + 12 * 8
+    # 8 int32 + 3 float + 1 int32 + 14 pointers
+    assert C.sizeof(_abi.GsrInputs) == 8 * 4 + 4 * 4 + 14 * 8
 
 
 def test_higher_msb_matches_reference_semantics():
