@@ -103,6 +103,9 @@ def sharded_step(views: Sequence, render_backward: Callable[[object], Optional[t
     return total
 
 
+_pipelines = {}  # one views.ViewPipeline per device, created on first use
+
+
 def sharded_accumulate_step(settings: Sequence, inputs: Dict[str, torch.Tensor],
                             loss_fn: Callable[[torch.Tensor, int], torch.Tensor], bucket: FlatGradBucket,
                             rank: Optional[int] = None, world: Optional[int] = None, group=None,
@@ -120,9 +123,6 @@ def sharded_accumulate_step(settings: Sequence, inputs: Dict[str, torch.Tensor],
     call `backprop_inputs(inputs, bucket)` afterwards: the activation backward then runs once per step instead of
     once per camera.
     """
-    if forward_view is None or backward_view is None:
-        from . import views as _v
-        forward_view, backward_view = forward_view or _v.forward_view, backward_view or _v.backward_view
     on = dist.is_available() and dist.is_initialized()
     rank = (dist.get_rank(group) if on else 0) if rank is None else rank
     world = (dist.get_world_size(group) if on else 1) if world is None else world
@@ -132,14 +132,36 @@ def sharded_accumulate_step(settings: Sequence, inputs: Dict[str, torch.Tensor],
     grads = {n: bucket.grad(n) for n in inputs}
     plain = {n: t.detach() for n, t in inputs.items()}
     total = torch.zeros((), dtype=bucket.flat.dtype, device=bucket.flat.device)
-    for k in shard_views(len(settings), rank, world):
-        image, _radii, state = forward_view(settings[k], plain["means3D"], plain["opacities"],
-                                            **{n: t for n, t in plain.items() if n not in ("means3D", "opacities")})
-        image = image.detach().requires_grad_(True)
-        loss = loss_fn(image, k)
-        (dL_dimage,) = torch.autograd.grad(loss, image)
-        backward_view(state, dL_dimage, grads)
-        total = total + loss.detach().to(total.dtype)
+    mine = shard_views(len(settings), rank, world)
+    extra = {n: t for n, t in plain.items() if n not in ("means3D", "opacities")}
+    if forward_view is None and backward_view is None:
+        # the three-stream pipeline: next camera's preprocess / sorts under this camera's blending kernels
+        from . import views as _v
+        dev = plain["means3D"].device
+        vp = _pipelines.get(dev)
+        if vp is None:
+            vp = _pipelines[dev] = _v.ViewPipeline(dev)
+        losses = []
+
+        def dL_fn(image, i):
+            image = image.requires_grad_(True)
+            loss = loss_fn(image, mine[i])
+            losses.append(loss.detach())
+            return torch.autograd.grad(loss, image)[0]
+        vp.step([settings[k] for k in mine], dL_fn, grads, plain["means3D"], plain["opacities"], **extra)
+        for l in losses:
+            total = total + l.to(total.dtype)
+    else:
+        if forward_view is None or backward_view is None:
+            from . import views as _v
+            forward_view, backward_view = forward_view or _v.forward_view, backward_view or _v.backward_view
+        for k in mine:
+            image, _radii, state = forward_view(settings[k], plain["means3D"], plain["opacities"], **extra)
+            image = image.detach().requires_grad_(True)
+            loss = loss_fn(image, k)
+            (dL_dimage,) = torch.autograd.grad(loss, image)
+            backward_view(state, dL_dimage, grads)
+            total = total + loss.detach().to(total.dtype)
     bucket.all_reduce(group)
     if on and world > 1:
         dist.all_reduce(total, op=dist.ReduceOp.SUM, group=group)

@@ -71,7 +71,8 @@ class _Slot:
 
 class HostStepPipeline:
     def __init__(self, P: int, M: int, W: int, H: int, n_views: int, tanfovx: float, tanfovy: float, sh_degree: int,
-                 device, bg: Optional[torch.Tensor] = None, depth: int = 2, group=None, overlap: bool = True):
+                 device, bg: Optional[torch.Tensor] = None, depth: int = 2, group=None, overlap: bool = True,
+                 share_over_nvlink: bool = True):
         if depth < 1:
             raise ValueError("depth must be >= 1")
         self.P, self.M, self.W, self.H, self.n_views = P, M, W, H, n_views
@@ -84,18 +85,31 @@ class HostStepPipeline:
         self.s_in = torch.cuda.Stream(self.dev)
         self.s_out = torch.cuda.Stream(self.dev)
         self.group = group
+        # With several ranks on one box every rank would pull the same 236 B/Gaussian attribute vector over PCIe and
+        # push the same all-reduced gradient back: instead rank 0 uploads the attributes once and broadcasts them over
+        # NVLink, and only rank 0 copies the (identical) gradient to the host.
+        self.world, self.rank = 1, 0
+        if group is not False:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.share = bool(share_over_nvlink) and self.world > 1
         self.views = _views.ViewPipeline(self.dev, overlap=overlap)
         self.n_submitted = 0
         self.staged = None  # slot whose inputs are in flight and whose compute has not been issued yet
-        self.h2d_bytes = 4 * (self.n_param + n_views * 36 + n_views * 3 * H * W)
-        self.d2h_bytes = 4 * self.n_param
+        self.h2d_bytes = 4 * (self.n_param + n_views * 36 + n_views * 3 * H * W)  # rank 0; others skip n_param if shared
+        self.d2h_bytes = 4 * self.n_param                                         # rank 0
 
     # -- stages ---------------------------------------------------------------------------------------------
     def _copy_in(self, slot, host_param, host_cam, host_dL):
         with torch.cuda.stream(self.s_in):
             if slot.used:
                 self.s_in.wait_event(slot.ev_compute)  # the previous step in this slot has finished reading
-            slot.param.copy_(host_param, non_blocking=True)
+            if not self.share or self.rank == 0:
+                slot.param.copy_(host_param, non_blocking=True)
+            if self.share:
+                import torch.distributed as dist
+                dist.broadcast(slot.param, src=dist.get_global_rank(self.group, 0) if self.group else 0, group=self.group)
             slot.cam.copy_(host_cam, non_blocking=True)
             slot.dL.copy_(host_dL, non_blocking=True)
             slot.ev_in.record(self.s_in)
@@ -125,7 +139,8 @@ class HostStepPipeline:
     def _copy_out(self, slot, host_grad):
         with torch.cuda.stream(self.s_out):
             self.s_out.wait_event(slot.ev_compute)
-            host_grad.copy_(slot.grad, non_blocking=True)
+            if not self.share or self.rank == 0:
+                host_grad.copy_(slot.grad, non_blocking=True)
             slot.ev_out.record(self.s_out)
         slot.pending_out = host_grad
         slot.used = True

@@ -494,7 +494,9 @@ def run_gsr(args):
         e2e = {"value": views_total / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(wl.pipe.h2d_bytes),
                "d2h_bytes_per_step": int(wl.pipe.d2h_bytes), "ms_per_step": ms_e / args.steps,
                "how": "pipeline.HostStepPipeline depth 2: H2D of step i+1 and D2H of step i-1 overlap the compute of "
-                      "step i; all copies, the pipeline fill and the drain are inside the timed region",
+                      "step i; all copies, the pipeline fill and the drain are inside the timed region"
+                      + ("; with N > 1 rank 0 uploads the attribute vector once and broadcasts it over NVLink, every rank uploads "
+                         "its own cameras and dL/dimage, rank 0 reads the all-reduced gradient back" if world > 1 else ""),
                "host_cpus": numa_cpus,
                "serial": {"value": world * len(wl.cams) / (ms_s * 1e-3), "unit": UNIT, "ms_per_step": ms_s,
                           "how": "same step, copies and compute on one stream, nothing overlapped"}}
