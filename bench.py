@@ -35,7 +35,13 @@ for _p in (ROOT, PKG):
 
 import numpy as np  # noqa: E402
 
-METRIC = "fwd+bwd views/sec at 1080p, 1M Gaussians"
+METRIC = "fwd+bwd views/sec at 1080p, 1M Gaussians"  # the default workload (C2); other --workload values are named below
+
+
+def metric_name(P, W, H):
+    if (W, H) == (1920, 1080) and P == 1_000_000:
+        return METRIC
+    return f"fwd+bwd views/sec at {W}x{H}, {P / 1e6:g}M Gaussians"
 UNIT = "views/s"
 
 
@@ -167,7 +173,7 @@ def run_reference(args):
     c = scene["cam"]
     sample = f"{n} full view(s) fwd+bwd of {args.workload} (P={scene['P']}, {c['image_width']}x{c['image_height']}), {warmup} warm-up"
     line = {
-        "impl": "reference", "metric": METRIC, "value": vps, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "impl": "reference", "metric": metric_name(scene["P"], c["image_width"], c["image_height"]), "value": vps, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {scene['P']} Gaussians SH3, {c['image_width']}x{c['image_height']}, fwd+bwd",
@@ -527,7 +533,7 @@ def run_gsr(args):
                     "peak_source": "148 SM x 128 FP32 lanes x sm_max_mhz; HBM " + peak_src}
     c = wl.scene["cam"]
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "metric": metric_name(wl.P, wl.W, wl.H), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {wl.P} Gaussians SH3, {c['image_width']}x{c['image_height']}, fwd+bwd",
