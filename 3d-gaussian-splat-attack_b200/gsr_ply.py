@@ -17,7 +17,7 @@ import re
 
 import numpy as np
 
-__all__ = ["save_ply", "load_ply", "activated", "property_names"]
+__all__ = ["save_ply", "load_ply", "combine_splats", "activated", "property_names"]
 
 _TYPES = {"float": "<f4", "float32": "<f4", "double": "<f8", "float64": "<f8", "uchar": "u1", "uint8": "u1",
           "char": "i1", "int8": "i1", "ushort": "<u2", "uint16": "<u2", "short": "<i2", "int16": "<i2",
@@ -128,6 +128,46 @@ def load_ply(path, max_sh_degree=3, num_objects=16):
     c = np.ascontiguousarray
     return dict(xyz=c(xyz), features_dc=c(dc), features_rest=c(rest), opacity=c(opacity), scaling=c(scaling),
                 rotation=c(rotation), objects_dc=objects)
+
+
+def combine_splats(paths, max_sh_degree=3, num_objects=16, reference_masks=False):
+    """combine_splats (scene/gaussian_model.py:469-556): concatenate several PLY scenes in the order given and
+    return (scene, masks).  As in the reference, f_rest_* columns are zero-padded or truncated to 3*((D+1)^2-1)
+    (a degree-0 splat can join a degree-3 scene), files need no obj_dc_* and the combined object features are all
+    zero.  masks[k] is a bool vector over the COMBINED scene that is True on file k's Gaussians -- what the masked
+    attacks index with.  The reference allocates mask k with only file k's length and sets [start, start+n_k) in
+    it (:539-541), so every mask after the first comes out short and partly or wholly False; pass
+    reference_masks=True to get exactly those."""
+    if not paths:
+        raise ValueError("No valid .ply files were loaded.")  # :545
+    n_rest = 3 * ((max_sh_degree + 1) ** 2 - 1)
+    parts, counts = [], []
+    for path in paths:
+        v = _read_vertex_table(path)
+        names = v.dtype.names
+        col = lambda n: np.asarray(v[n], np.float32)
+        n = v.shape[0]
+        rest_names = _numbered(names, "f_rest_")
+        rest = np.stack([col(c) for c in rest_names], axis=1) if rest_names else np.zeros((n, 0), np.float32)
+        if rest.shape[1] < n_rest:
+            rest = np.hstack([rest, np.zeros((n, n_rest - rest.shape[1]), np.float32)])
+        rest = rest[:, :n_rest].reshape(n, 3, n_rest // 3).transpose(0, 2, 1)
+        parts.append(dict(
+            xyz=np.stack([col("x"), col("y"), col("z")], axis=1),
+            features_dc=np.stack([col("f_dc_0"), col("f_dc_1"), col("f_dc_2")], axis=1)[:, None, :],
+            features_rest=rest, opacity=col("opacity")[:, None],
+            scaling=np.stack([col(c) for c in _numbered(names, "scale_")], axis=1),
+            rotation=np.stack([col(c) for c in _numbered(names, "rot_")], axis=1),
+            objects_dc=np.zeros((n, 1, num_objects), np.float32)))
+        counts.append(n)
+    scene = {k: np.ascontiguousarray(np.concatenate([p[k] for p in parts], axis=0)) for k in parts[0]}
+    total, start, masks = sum(counts), 0, []
+    for n in counts:
+        m = np.zeros(n if reference_masks else total, bool)
+        m[start:start + n] = True
+        masks.append(m)
+        start += n
+    return scene, masks
 
 
 def activated(scene):

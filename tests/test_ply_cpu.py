@@ -81,3 +81,27 @@ def test_wrong_sh_count_asserts_and_activations(tmp_path):
     assert np.allclose(np.linalg.norm(a["rotations"], axis=1), 1.0, atol=1e-6)
     assert np.allclose(a["opacities"], 1 / (1 + np.exp(-s["opacity"])), atol=1e-6)
     assert np.allclose(a["scales"], np.exp(s["scaling"]), rtol=1e-6)
+
+
+def test_combine_splats_concatenates_pads_and_masks(tmp_path):
+    """combine_splats (scene/gaussian_model.py:469-556): order kept, f_rest padded, objects zero, masks per file."""
+    a, b = _scene(P=11, seed=1), _scene(P=7, M=4, seed=2)  # b is a degree-1 splat (9 f_rest columns)
+    pa, pb = str(tmp_path / "a.ply"), str(tmp_path / "b.ply")
+    gsr_ply.save_ply(pa, a)
+    gsr_ply.save_ply(pb, b)
+    s, masks = gsr_ply.combine_splats([pa, pb])
+    assert s["xyz"].shape == (18, 3) and s["features_rest"].shape == (18, 15, 3) and s["objects_dc"].shape == (18, 1, 16)
+    for k in ("xyz", "features_dc", "opacity", "scaling", "rotation"):
+        assert np.array_equal(s[k][:11], a[k]) and np.array_equal(s[k][11:], b[k]), k
+    assert np.array_equal(s["features_rest"][:11], a["features_rest"])
+    # the 9 stored columns are channel-major with 3 per channel; padded to 45 and re-read as (3, 15): the
+    # reference's own reshape, so the first 9 flat values are b's, the rest zero
+    flat = s["features_rest"][11:].transpose(0, 2, 1).reshape(7, 45)
+    assert np.array_equal(flat[:, :9], b["features_rest"].transpose(0, 2, 1).reshape(7, 9)) and not flat[:, 9:].any()
+    assert not s["objects_dc"].any()
+    assert [m.shape for m in masks] == [(18,), (18,)]
+    assert masks[0][:11].all() and not masks[0][11:].any() and masks[1][11:].all() and not masks[1][:11].any()
+    _, ref = gsr_ply.combine_splats([pa, pb], reference_masks=True)
+    assert ref[0].shape == (11,) and ref[0].all() and ref[1].shape == (7,) and not ref[1].any()
+    with pytest.raises(ValueError):
+        gsr_ply.combine_splats([])
