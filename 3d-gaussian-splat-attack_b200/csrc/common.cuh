@@ -183,6 +183,28 @@ __device__ __forceinline__ float4 act_normalize(float4 q, float* inv_norm_out) {
   if (inv_norm_out) *inv_norm_out = 1.0f / d;
   return make_float4(__fdiv_rn(q.x, d), __fdiv_rn(q.y, d), __fdiv_rn(q.z, d), __fdiv_rn(q.w, d));
 }
+// The (P, 15, 3) SH "rest" block has 180-byte rows: only 4-byte aligned, but row idx begins exactly (idx & 3) floats
+// after a 16-byte boundary (45 = 1 mod 4), so the 48-float window that starts at that boundary covers the row and is
+// moved with 12 aligned 16-byte accesses; the up to 3 floats either side belong to the neighbouring rows (loads ignore
+// them, reductions add 0 to them).  Not for the last row (its window would end past the array) or an unaligned base.
+__device__ __forceinline__ bool rest_window_ok(const void* base, size_t idx, int P) {
+  return (reinterpret_cast<uintptr_t>(base) & 15) == 0 && idx + 1 < (size_t)P;
+}
+// shv[3 .. 47] <- row idx of the rest block (shv[0 .. 2], the DC coefficient, is the caller's)
+__device__ __forceinline__ void load_rest_row(const float* __restrict__ rest, size_t idx, float* shv) {
+  const int s = (int)(idx & 3);
+  const float4* wp = reinterpret_cast<const float4*>(rest + 45 * idx - s);
+  float w[48], t[47];
+#pragma unroll
+  for (int k = 0; k < 12; k++) {
+    const float4 v = __ldg(wp + k);
+    w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+  }
+#pragma unroll
+  for (int m = 0; m < 47; m++) t[m] = (s & 1) ? w[m + 1] : w[m];
+#pragma unroll
+  for (int m = 0; m < 45; m++) shv[3 + m] = (s & 2) ? t[m + 2] : t[m];
+}
 // coefficient i (0 .. 3M-1, coefficient-major, channel-minor) of Gaussian idx from either SH layout
 __device__ __forceinline__ float sh_coeff(const gsr_inputs& in, size_t idx, int i) {
   if (in.shs_rest) return i < 3 ? __ldg(in.shs + 3 * idx + i) : __ldg(in.shs_rest + (size_t)(in.M - 1) * 3 * idx + (i - 3));

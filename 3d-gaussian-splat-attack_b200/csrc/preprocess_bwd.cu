@@ -91,7 +91,13 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
     if (SPLIT) {  // DC / rest blocks where the model keeps them (4-byte aligned rows)
       const int ncoef = 3 * (in.D + 1) * (in.D + 1);
 #pragma unroll
-      for (int k = 0; k < 48; k++) shv[k] = k < ncoef ? sh_coeff(in, (size_t)idx, k) : 0.f;
+      for (int k = 0; k < 3; k++) shv[k] = __ldg(in.shs + 3 * (size_t)idx + k);
+      if (rest_window_ok(in.shs_rest, (size_t)idx, in.P)) {
+        load_rest_row(in.shs_rest, (size_t)idx, shv);
+      } else {
+#pragma unroll
+        for (int k = 3; k < 48; k++) shv[k] = k < ncoef ? sh_coeff(in, (size_t)idx, k) : 0.f;
+      }
     } else {
       const float4* sp0 = reinterpret_cast<const float4*>(in.shs) + (size_t)idx * 12;
 #pragma unroll
@@ -218,7 +224,25 @@ preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, 
         for (int k = 0; k < 48; k++) outv[k] = 0.f;
         ddir = sh_backward(in.D, x, y, z, dRGB, [&](int i) { return V3{shv[3 * i], shv[3 * i + 1], shv[3 * i + 2]}; },
                            [&](int i, float w) { outv[3 * i] = w * dRGB.x; outv[3 * i + 1] = w * dRGB.y; outv[3 * i + 2] = w * dRGB.z; });
-        if (SPLIT) {
+        if (SPLIT && ACC && in.D >= 3 && rest_window_ok(in.dL_dshs_rest, (size_t)idx, in.P)) {
+          // DC: 3 scalar reductions; rest row: its aligned 48-float window, zeros outside the row (see common.cuh)
+#pragma unroll
+          for (int c2 = 0; c2 < 3; c2++) atomicAdd(dL_dsh + 3 * (size_t)idx + c2, outv[c2]);
+          const int s = idx & 3;
+          auto ext = [&](int j) { return (j >= 0 && j < 45) ? outv[3 + j] : 0.f; };  // j is a constant after unrolling
+          float4* wp = reinterpret_cast<float4*>(in.dL_dshs_rest + (size_t)45 * idx - s);
+#pragma unroll
+          for (int k = 0; k < 12; k++) {
+            float o[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              const int j = 4 * k + e;
+              const float t0 = (s & 1) ? ext(j - 1) : ext(j), t2 = (s & 1) ? ext(j - 3) : ext(j - 2);
+              o[e] = (s & 2) ? t2 : t0;
+            }
+            red_add4(wp + k, make_float4(o[0], o[1], o[2], o[3]));
+          }
+        } else if (SPLIT) {
           const int nc = (in.D + 1) * (in.D + 1);
 #pragma unroll
           for (int k = 0; k < 16; k++) {

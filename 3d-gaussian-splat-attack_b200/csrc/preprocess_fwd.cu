@@ -170,6 +170,8 @@ __device__ __forceinline__ void sh_to_rgb(int deg, float px, float py, float pz,
   }
 }
 
+// EXT: the N3 inputs (split SH blocks, raw parameters) -- compiled out of the standard kernel, as in preprocess_bwd
+template <bool EXT>
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32_t* flags,
                       uint32_t* __restrict__ dkeys) {
@@ -201,7 +203,7 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
       } else {
         float3 s = make_float3(in.scales[3 * idx], in.scales[3 * idx + 1], in.scales[3 * idx + 2]);
         float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
-        if (in.raw_params) {  // exp / normalize activations applied here (scene/gaussian_model.py:97-105)
+        if (EXT && in.raw_params) {  // exp / normalize activations applied here (scene/gaussian_model.py:97-105)
           s = make_float3(expf(s.x), expf(s.y), expf(s.z));
           q = act_normalize(q, nullptr);
         }
@@ -235,13 +237,19 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
             rgb[0] = in.colors_precomp[3 * (size_t)idx];
             rgb[1] = in.colors_precomp[3 * (size_t)idx + 1];
             rgb[2] = in.colors_precomp[3 * (size_t)idx + 2];
-          } else if (in.shs_rest) {
+          } else if (EXT && in.shs_rest) {
             // DC and rest blocks read where the model keeps them (no torch.cat): rows are only 4-byte aligned
             float shv[48];
             const int ncoef = 3 * (in.D + 1) * (in.D + 1);
             if (in.M == 16) {
 #pragma unroll
-              for (int k = 0; k < 48; k++) shv[k] = k < ncoef ? sh_coeff(in, (size_t)idx, k) : 0.f;
+              for (int k = 0; k < 3; k++) shv[k] = __ldg(in.shs + 3 * (size_t)idx + k);
+              if (rest_window_ok(in.shs_rest, (size_t)idx, in.P)) {
+                load_rest_row(in.shs_rest, (size_t)idx, shv);
+              } else {
+#pragma unroll
+                for (int k = 3; k < 48; k++) shv[k] = k < ncoef ? sh_coeff(in, (size_t)idx, k) : 0.f;
+              }
               sh_to_rgb(in.D, px, py, pz, cam.campos, [&](int i) { return shv[i]; }, rgb, cbits);
             } else {
               sh_to_rgb(in.D, px, py, pz, cam.campos, [&](int i) { return sh_coeff(in, (size_t)idx, i); }, rgb, cbits);
@@ -261,7 +269,7 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
             const float* sp = in.shs + (size_t)idx * in.M * 3;
             sh_to_rgb(in.D, px, py, pz, cam.campos, [&](int i) { return __ldg(sp + i); }, rgb, cbits);
           }
-          const float op = in.raw_params ? act_sigmoid(in.opacities[idx]) : in.opacities[idx];
+          const float op = (EXT && in.raw_params) ? act_sigmoid(in.opacities[idx]) : in.opacities[idx];
           g.depths[idx] = depth;
           g.means2D[idx] = make_float2(pix_x, pix_y);
           g.conic_opacity[idx] = make_float4(mul(cov.z, det_inv), mul(det_inv, -cov.y), mul(cov.x, det_inv), op);
@@ -302,7 +310,10 @@ int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch
   const int nblocks = (in.P + PRE_THREADS - 1) / PRE_THREADS;
   GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_status, 0, s.scan_zero_bytes, st));
   (void)num_rendered_dev;  // written by the depth-order scan (launch_sorted_scan)
-  preprocess_fwd_kernel<<<nblocks, PRE_THREADS, 0, st>>>(in, g, radii, s.flags, s.dkeys_a);
+  if (in.shs_rest != nullptr || in.raw_params != 0)
+    preprocess_fwd_kernel<true><<<nblocks, PRE_THREADS, 0, st>>>(in, g, radii, s.flags, s.dkeys_a);
+  else
+    preprocess_fwd_kernel<false><<<nblocks, PRE_THREADS, 0, st>>>(in, g, radii, s.flags, s.dkeys_a);
   GSR_LAUNCH_CHECK("preprocess_fwd_kernel");
   return GSR_OK;
 }
