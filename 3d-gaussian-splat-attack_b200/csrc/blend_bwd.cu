@@ -42,8 +42,6 @@ constexpr int NWARP = TILE_PIX / 32;
 struct BwdWarp {
   float2 panel[GRP][PANEL_STRIDE];  // [group slot][pixel lane] = (alpha*T, G*dL/dalpha); 0 when the pair does not contribute
   float4 pix[32];                   // dL/dpixel (r, g, b, -) of each pixel lane
-  uint8_t q[32];                    // kept batch slots of the current cull round
-  uint8_t gj[GRP];                  // batch slot of each group entry
 };
 struct BwdSmem {
   BlendStage S;
@@ -68,6 +66,9 @@ __device__ __forceinline__ float warp_sum8(const float* v, int lane) {
   y += __shfl_xor_sync(0xffffffffu, y, 1);
   return y;
 }
+__device__ __forceinline__ void red_add4(float* p, float x, float y, float z, float w) {  // 16-byte aligned p
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
 __device__ __forceinline__ float fast_exp(float x) {  // ex2.approx(x log2 e): 2 ulp, enough for gradients
   float r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
@@ -81,15 +82,17 @@ __device__ __forceinline__ float fast_rcp(float x) {
 
 // Phase 2: lane (e = lane % GRP, h = lane / GRP) sums, over pixel lanes h*GRP .. h*GRP+GRP-1, the 9 per-Gaussian
 // quantities of group entry e; the 32/GRP partial sums are joined with shuffles and lanes < ng issue the REDs.
-__device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int lane, float wx0f, float wy0f,
-                                            float* __restrict__ accum) {
+// slot_j: lane e < ng holds the batch slot of group entry e (kept in a register, not in shared memory).
+__device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int lane, int slot_j, float wx0f,
+                                            float wy0f, float* __restrict__ accum) {
   __syncwarp();
   const int e = lane & (GRP - 1), h = lane / GRP;
   float cx = 0.f, cy = 0.f;
   uint32_t g = 0;
+  const int j = __shfl_sync(0xffffffffu, slot_j, e);
   if (e < ng) {
-    const int j = Wp.gj[e];
-    cx = M.S.a[j].x; cy = M.S.a[j].y; g = M.id[j];
+    const float2 cxy = *reinterpret_cast<const float2*>(&M.S.a[j]);
+    cx = cxy.x; cy = cxy.y; g = M.id[j];
   }
   const float2* row = &Wp.panel[e][h * GRP];
   const float4* pix = &Wp.pix[h * GRP];
@@ -127,10 +130,9 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
     myy += __shfl_xor_sync(0xffffffffu, myy, off);
   }
   if (lane < ng) {
-    float* dst = accum + (size_t)g * 12;
-    atomicAdd(dst + 0, s0); atomicAdd(dst + 1, s1); atomicAdd(dst + 2, s2);
-    atomicAdd(dst + 3, m1); atomicAdd(dst + 4, m2);
-    atomicAdd(dst + 5, mxx); atomicAdd(dst + 6, mxy); atomicAdd(dst + 7, myy);
+    float* dst = accum + (size_t)g * 12;  // 48-byte rows: two 16-byte vector reductions + one scalar
+    red_add4(dst, s0, s1, s2, m1);
+    red_add4(dst + 4, m2, mxx, mxy, myy);
     atomicAdd(dst + 8, m0);
   }
   __syncwarp();
@@ -150,7 +152,6 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   BwdWarp& Wp = M.w[warp];
-  const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t wx0 = blockIdx.x * TILE_X + (warp & 1) * WARP_W, wy0 = blockIdx.y * TILE_Y + (warp >> 1) * WARP_H;
   const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
@@ -177,7 +178,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   __syncthreads();
   const uint32_t n_live = min(M.smax, range.y - range.x);  // entries [0, n_live) can matter to this tile
 
-  int ng = 0;  // entries in this warp's current group (warp-uniform)
+  int ng = 0;      // entries in this warp's current group (warp-uniform)
+  int slot_j = 0;  // lane e: batch slot of group entry e
   // batches walk the list back to front: slot j of a batch holds list position n_live-1-done_cnt-j
   for (uint32_t done_cnt = 0; done_cnt < n_live; done_cnt += BLEND_BATCH) {
     __syncthreads();
@@ -195,11 +197,9 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       if (jl < nb && top - jl < warp_last) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
       const uint32_t mask = __ballot_sync(0xffffffffu, keep);
       GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
-      if (keep) Wp.q[__popc(mask & lt_mask)] = (uint8_t)jl;
-      __syncwarp();
-      const int nk = __popc(mask);
-      for (int i = 0; i < nk; i++) {
-        const int j = Wp.q[i];
+      // kept slots in ascending order straight from the ballot (no queue in shared memory)
+      for (uint32_t rest = mask; rest != 0; rest &= rest - 1) {
+        const int j = r + __ffs(rest) - 1;
         const float4 a = S.a[j];
         const float4 b = S.b[j];
         const uint32_t pos = top - j;
@@ -257,7 +257,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           wg = G * dL_dalpha;
         }
         Wp.panel[ng][lane] = make_float2(wc, wg);
-        if (lane == 0) Wp.gj[ng] = (uint8_t)j;
+        if (lane == ng) slot_j = j;
         if (K > 0) {
           const uint32_t g = M.id[j];
           const float o8a = warp_sum8(vo, lane), o8b = warp_sum8(vo + (K > 8 ? 8 : 0), lane);
@@ -266,11 +266,11 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
             if (K > 8) atomicAdd(dL_dobj + (size_t)g * K + 8 + (lane >> 2), o8b);
           }
         }
-        if (++ng == GRP) { flush_group(M, Wp, ng, lane, wx0f, wy0f, accum); ng = 0; }
+        if (++ng == GRP) { flush_group(M, Wp, ng, lane, slot_j, wx0f, wy0f, accum); ng = 0; }
       }
     }
     // the staged batch is about to be replaced: finish the partial group that refers to it
-    if (ng > 0) { flush_group(M, Wp, ng, lane, wx0f, wy0f, accum); ng = 0; }
+    if (ng > 0) { flush_group(M, Wp, ng, lane, slot_j, wx0f, wy0f, accum); ng = 0; }
   }
 }
 
