@@ -194,7 +194,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     for (int r = 0; r < nb; r += 32) {
       const int jl = r + lane;
       bool keep = false;
-      if (jl < nb && top - jl < warp_last) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
+      if (jl < nb && top - jl < warp_last) keep = rect_may_contribute(S.a[jl], S.b[jl], wx0f, wy0f);
       const uint32_t mask = __ballot_sync(0xffffffffu, keep);
       GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
       // kept slots in ascending order straight from the ballot (no queue in shared memory)
@@ -205,12 +205,13 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         const uint32_t pos = top - j;
         const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
         const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-        bool hit = pos < my_last && !(power > 0.0f || power < b.z);
+        bool hit = pos < my_last && !(power > 0.0f || power < b.y);
+        const float4 c = S.c[j];
 #ifdef GSR_BWD_EXACT_EXP
         float G = 0.f, alpha = 0.f;
         if (hit) {
           G = expf(power);
-          alpha = fminf(0.99f, fpx::mul(b.y, G));
+          alpha = fminf(0.99f, fpx::mul(c.x, G));
           hit = !(alpha < 1.0f / 255.0f);
         }
 #else
@@ -219,11 +220,11 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         // when some lane's alpha lands next to the 1/255 threshold (rare) the warp redoes it with the forward's
         // arithmetic.
         float G = fast_exp(power);
-        float alpha = fminf(0.99f, b.y * G);
+        float alpha = fminf(0.99f, c.x * G);
         const bool near = hit && fabsf(alpha - 1.0f / 255.0f) < 4e-8f;
         if (__any_sync(0xffffffffu, near)) {
           const float Ge = expf(fminf(power, 0.f));
-          if (near) { G = Ge; alpha = fminf(0.99f, fpx::mul(b.y, Ge)); }
+          if (near) { G = Ge; alpha = fminf(0.99f, fpx::mul(c.x, Ge)); }
         }
         hit = hit && !(alpha < 1.0f / 255.0f);
 #endif
@@ -239,8 +240,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           // dC/dalpha_j = T_j c_j - (sum_{k behind j} c_k alpha_k T_k + T_final bg) / (1 - alpha_j); dotted with
           // dL/dpixel the sum is ONE running scalar `behind` (the reference carries the same quantity per
           // channel, normalised, as accum_rec: backward.cu:499-521)
-          const float4 c = S.c[j];
-          float cd = b.w * dpix[0] + c.x * dpix[1] + c.y * dpix[2];
+          float cd = c.y * dpix[0] + c.z * dpix[1] + c.w * dpix[2];
           const float inv = fast_rcp(1.f - alpha);
           T = T * inv;
           wc = alpha * T;

@@ -39,8 +39,8 @@ __device__ __forceinline__ float gauss_power(float dx, float dy, float A, float 
 // One staged list entry (shared memory, SoA of vector words).
 struct BlendStage {
   float4 a[BLEND_BATCH];  // x, y, conic A, conic B
-  float4 b[BLEND_BATCH];  // conic C, opacity, power threshold, r
-  float4 c[BLEND_BATCH];  // g, b, -B/C, -B/A
+  float4 b[BLEND_BATCH];  // conic C, power threshold, -B/C, -B/A   (a and b are all the rectangle cull reads)
+  float4 c[BLEND_BATCH];  // opacity, r, g, b
 };
 
 __device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g, const float2* __restrict__ means2D,
@@ -50,8 +50,8 @@ __device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g,
   const float4 co = conic_opacity[g];
   const float4 ct = rgb_thr[g];
   S.a[slot] = make_float4(xy.x, xy.y, co.x, co.y);
-  S.b[slot] = make_float4(co.z, co.w, ct.w, ct.x);
-  S.c[slot] = make_float4(ct.y, ct.z, __fdividef(-co.y, co.z), __fdividef(-co.y, co.x));
+  S.b[slot] = make_float4(co.z, ct.w, __fdividef(-co.y, co.z), __fdividef(-co.y, co.x));
+  S.c[slot] = make_float4(co.w, ct.x, ct.y, ct.z);
 }
 
 // Conservative test of one list entry against a warp's pixel rectangle [x0, x0+WARP_W-1] x [y0, y0+WARP_H-1]:
@@ -62,15 +62,14 @@ __device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g,
 // both this evaluation and the per-pixel one (each <= ~5e-7 * S, S = sum of the magnitudes of the terms,
 // bounded over the rectangle by Smax), so a pair that passes per pixel is never culled here.  NaNs compare
 // false and are kept.
-__device__ __forceinline__ bool rect_may_contribute(const float4 a, const float4 b, const float4 c, float x0,
-                                                    float y0) {
-  const float A = a.z, B = a.w, C = b.x, thr = b.z;
+__device__ __forceinline__ bool rect_may_contribute(const float4 a, const float4 b, float x0, float y0) {
+  const float A = a.z, B = a.w, C = b.x, thr = b.y;
   const float ux0 = x0 - a.x, ux1 = ux0 + (float)(WARP_W - 1);
   const float vy0 = y0 - a.y, vy1 = vy0 + (float)(WARP_H - 1);
   const float u1 = fminf(fmaxf(0.f, ux0), ux1);
-  const float v1 = fminf(fmaxf(c.z * u1, vy0), vy1);
+  const float v1 = fminf(fmaxf(b.z * u1, vy0), vy1);
   const float v2 = fminf(fmaxf(0.f, vy0), vy1);
-  const float u2 = fminf(fmaxf(c.w * v2, ux0), ux1);
+  const float u2 = fminf(fmaxf(b.w * v2, ux0), ux1);
   const float f1 = -0.5f * (A * u1 * u1 + C * v1 * v1) - B * u1 * v1;
   const float f2 = -0.5f * (A * u2 * u2 + C * v2 * v2) - B * u2 * v2;
   const float um = fmaxf(fabsf(ux0), fabsf(ux1)), vm = fmaxf(fabsf(vy0), fabsf(vy1));

@@ -60,7 +60,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       if (__all_sync(0xffffffffu, done)) break;
       const int jl = r + lane;
       bool keep = false;
-      if (jl < nb) keep = rect_may_contribute(S.a[jl], S.b[jl], S.c[jl], wx0f, wy0f);
+      if (jl < nb) keep = rect_may_contribute(S.a[jl], S.b[jl], wx0f, wy0f);
       const uint32_t mask = __ballot_sync(0xffffffffu, keep);
       GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
       // compact the kept slots into this warp's queue (list order is preserved)
@@ -76,15 +76,15 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         const float4 b = S.b[j];
         const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
         const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-        if (done || power > 0.0f || power < b.z) continue;
-        const float alpha = fminf(0.99f, fpx::mul(b.y, expf(power)));
+        if (done || power > 0.0f || power < b.y) continue;
+        const float4 c = S.c[j];
+        const float alpha = fminf(0.99f, fpx::mul(c.x, expf(power)));
         if (alpha < 1.0f / 255.0f) continue;
         const float test_T = fpx::mul(T, fpx::sub(1.0f, alpha));
         if (test_T < 0.0001f) { done = true; continue; }
-        const float4 c = S.c[j];
-        C0 = fpx::fma_(T, fpx::mul(alpha, b.w), C0);
-        C1 = fpx::fma_(T, fpx::mul(alpha, c.x), C1);
-        C2 = fpx::fma_(T, fpx::mul(alpha, c.y), C2);
+        C0 = fpx::fma_(T, fpx::mul(alpha, c.y), C0);
+        C1 = fpx::fma_(T, fpx::mul(alpha, c.z), C1);
+        C2 = fpx::fma_(T, fpx::mul(alpha, c.w), C2);
         if (K > 0) {
           const float* f = obj_feats + (size_t)s_id[j] * K;
 #pragma unroll
