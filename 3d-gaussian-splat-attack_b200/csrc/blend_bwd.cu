@@ -41,7 +41,8 @@ constexpr int NWARP = TILE_PIX / 32;
 
 struct BwdWarp {
   float2 panel[GRP][PANEL_STRIDE];  // [group slot][pixel lane] = (alpha*T, G*dL/dalpha); 0 when the pair does not contribute
-  float4 pix[32];                   // dL/dpixel (r, g, b, -) of each pixel lane
+  float2 pix_rg[32];                // dL/dpixel (r, g) and (b) of each pixel lane: an 8-byte + a 4-byte read cost 3
+  float pix_b[32];                  // wavefronts where one 16-byte read with four distinct addresses costs 4
 };
 struct BwdSmem {
   BlendStage S;
@@ -95,14 +96,16 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
     cx = cxy.x; cy = cxy.y; g = M.id[j];
   }
   const float2* row = &Wp.panel[e][h * GRP];
-  const float4* pix = &Wp.pix[h * GRP];
+  const float2* pix_rg = &Wp.pix_rg[h * GRP];
+  const float* pix_b = &Wp.pix_b[h * GRP];
   // raw moments of w in the lane's local pixel coordinates (lx = 0..7, r = row inside the lane's strip): the
   // coordinates are compile-time constants, so each sum is one FFMA/FADD per pixel (none where the factor is 0)
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, M0 = 0.f, Mx = 0.f, My = 0.f, Mxx = 0.f, Mxy = 0.f;
 #pragma unroll
   for (int i = 0; i < GRP; i++) {
     const float2 pr = row[i];
-    const float4 dp = pix[i];
+    const float2 rg = pix_rg[i];
+    const float4 dp = make_float4(rg.x, rg.y, pix_b[i], 0.f);
     const int lx = i & 7, r = i >> 3;
     s0 = fmaf(pr.x, dp.x, s0); s1 = fmaf(pr.x, dp.y, s1); s2 = fmaf(pr.x, dp.z, s2);
     M0 += pr.y;
@@ -164,7 +167,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   float T = T_final;
   float dpix[3] = {0.f, 0.f, 0.f};
   if (inside) { dpix[0] = dL_dpix[pid]; dpix[1] = dL_dpix[HW + pid]; dpix[2] = dL_dpix[2 * HW + pid]; }
-  Wp.pix[lane] = make_float4(dpix[0], dpix[1], dpix[2], 0.f);
+  Wp.pix_rg[lane] = make_float2(dpix[0], dpix[1]);
+  Wp.pix_b[lane] = dpix[2];
   float dpo[K > 0 ? K : 1];
 #pragma unroll
   for (int k = 0; k < (K > 0 ? K : 1); k++) dpo[k] = (K > 0 && inside) ? dL_dobjpix[k * HW + pid] : 0.f;
@@ -192,20 +196,23 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     const int nb = (int)min((uint32_t)BLEND_BATCH, n_live - done_cnt);
     const uint32_t top = n_live - 1 - done_cnt;  // list position of slot 0
     for (int r = 0; r < nb; r += 32) {
-      const int jl = r + lane;
+      const int jl = r + 31 - lane;  // lane 31 tests the round's first slot: the ballot's leading bit is the next slot
       bool keep = false;
       if (jl < nb && top - jl < warp_last) keep = rect_may_contribute(S.a[jl], S.b[jl], wx0f, wy0f);
       const uint32_t mask = __ballot_sync(0xffffffffu, keep);
       GSR_STAT(0, 1); GSR_STAT(1, min(32, nb - r)); GSR_STAT(2, __popc(mask));
       // kept slots in ascending order straight from the ballot (no queue in shared memory)
-      for (uint32_t rest = mask; rest != 0; rest &= rest - 1) {
-        const int j = r + __ffs(rest) - 1;
+      for (uint32_t rest = mask; rest != 0;) {
+        const int lz = __clz(rest);
+        rest &= ~(0x80000000u >> lz);
+        const int j = r + lz;
         const float4 a = S.a[j];
         const float4 b = S.b[j];
         const uint32_t pos = top - j;
         const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
         const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-        bool hit = pos < my_last && !(power > 0.0f || power < b.y);
+        // (no `power < threshold` pre-test here: alpha is evaluated on every lane anyway and decides alone)
+        bool hit = pos < my_last && !(power > 0.0f);
         const float4 c = S.c[j];
 #ifdef GSR_BWD_EXACT_EXP
         float G = 0.f, alpha = 0.f;
@@ -224,7 +231,9 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         const bool near = hit && fabsf(alpha - 1.0f / 255.0f) < 4e-8f;
         if (__any_sync(0xffffffffu, near)) {
           const float Ge = expf(fminf(power, 0.f));
-          if (near) { G = Ge; alpha = fminf(0.99f, fpx::mul(c.x, Ge)); }
+          const float ae = fminf(0.99f, fpx::mul(c.x, Ge));
+          G = near ? Ge : G;
+          alpha = near ? ae : alpha;
         }
         hit = hit && !(alpha < 1.0f / 255.0f);
 #endif
