@@ -245,7 +245,18 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         float vo[K > 0 ? K : 1];
 #pragma unroll
         for (int k = 0; k < (K > 0 ? K : 1); k++) vo[k] = 0.f;
-        if (hit) {
+        if (K == 0) {
+          // straight-line form of the block below (no divergent region): a pair that does not contribute runs the
+          // same arithmetic with alpha = 0 and G = 0, which leaves T (x 1/(1-0)) and `behind` (+ cd*0) unchanged
+          const float ae = hit ? alpha : 0.f, Ge = hit ? G : 0.f;
+          const float cd = c.y * dpix[0] + c.z * dpix[1] + c.w * dpix[2];
+          const float inv = fast_rcp(1.f - ae);
+          T = T * inv;
+          wc = ae * T;
+          const float dL_dalpha = fmaf(T, cd, -behind * inv);
+          behind = fmaf(cd, wc, behind);
+          wg = Ge * dL_dalpha;
+        } else if (hit) {
           // dC/dalpha_j = T_j c_j - (sum_{k behind j} c_k alpha_k T_k + T_final bg) / (1 - alpha_j); dotted with
           // dL/dpixel the sum is ONE running scalar `behind` (the reference carries the same quantity per
           // channel, normalised, as accum_rec: backward.cu:499-521)

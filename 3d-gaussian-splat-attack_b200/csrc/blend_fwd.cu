@@ -76,25 +76,31 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         const float4 b = S.b[j];
         const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
         const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-        if (done || power > 0.0f || power < b.y) continue;
+        // Straight-line evaluation: every lane computes alpha, and the reference's three `continue`s
+        // (forward.cu:336-349) become predicates on the accumulation -- same values, same decisions, no divergent
+        // region in the loop (the per-Gaussian threshold pre-test is left to the rectangle cull).
         const float4 c = S.c[j];
+        const bool p1 = !done && !(power > 0.0f);
         const float alpha = fminf(0.99f, fpx::mul(c.x, expf(power)));
-        if (alpha < 1.0f / 255.0f) continue;
+        const bool p2 = p1 && !(alpha < 1.0f / 255.0f);
         const float test_T = fpx::mul(T, fpx::sub(1.0f, alpha));
-        if (test_T < 0.0001f) { done = true; continue; }
-        C0 = fpx::fma_(T, fpx::mul(alpha, c.y), C0);
-        C1 = fpx::fma_(T, fpx::mul(alpha, c.z), C1);
-        C2 = fpx::fma_(T, fpx::mul(alpha, c.w), C2);
-        if (K > 0) {
-          const float* f = obj_feats + (size_t)s_id[j] * K;
+        const bool stop = p2 && test_T < 0.0001f;
+        done = done || stop;
+        if (p2 && !stop) {
+          C0 = fpx::fma_(T, fpx::mul(alpha, c.y), C0);
+          C1 = fpx::fma_(T, fpx::mul(alpha, c.z), C1);
+          C2 = fpx::fma_(T, fpx::mul(alpha, c.w), C2);
+          if (K > 0) {
+            const float* f = obj_feats + (size_t)s_id[j] * K;
 #pragma unroll
-          for (int k = 0; k < K; k++) O[k] = fpx::fma_(T, fpx::mul(alpha, __ldg(f + k)), O[k]);
-        }
-        T = test_T;
-        last_contributor = first + j + 1;
+            for (int k = 0; k < K; k++) O[k] = fpx::fma_(T, fpx::mul(alpha, __ldg(f + k)), O[k]);
+          }
+          T = test_T;
+          last_contributor = first + j + 1;
 #ifdef GSR_STATS
-        atomicAdd(&g_blend_stats[4], 1ull);
+          atomicAdd(&g_blend_stats[4], 1ull);
 #endif
+        }
       }
     }
   }
