@@ -11,10 +11,11 @@
 //     dL/dmean2D, dL/dconic and dL/dopacity (same algebra as backward.cu:523-554);
 //   * the sum over the pixels of a Gaussian is done WITHOUT a per-entry cross-lane reduction:
 //     phase 1 (lane = pixel) runs the sequential per-pixel recurrence and writes (wc, w) of every
-//     (pixel, entry) pair of a group of 16 kept entries to a per-warp shared-memory panel;
-//     phase 2 (lane = entry x pixel-half) sweeps the panel, each lane accumulating the 9 sums of its
-//     own entry in registers, then one shuffle per value joins the two halves and one RED per value
-//     goes to the packed [P][12] accumulator (the reference issues 9 atomics per contributing pixel).
+//     (pixel, entry) pair of a group of GRP = 8 kept entries to a per-warp shared-memory panel;
+//     phase 2 (lane = entry x pixel-row) sweeps the panel, each lane accumulating the 9 sums of its
+//     own entry over one 8-pixel row in registers, two shuffles per value join the four rows, and the
+//     9 values go to the packed [P][12] accumulator as two 16-byte vector REDs + one scalar RED per
+//     (warp, entry) (the reference issues 9 atomics per contributing pixel).
 //   * the reference's three per-channel running colours (accum_rec, backward.cu:499-521) collapse into one
 //     running scalar: dL/dalpha_j = T_j (c_j . dL/dpixel) - behind_j / (1 - alpha_j), where behind_j =
 //     sum_{k behind j} (c_k . dL/dpixel) alpha_k T_k + T_final (bg . dL/dpixel)  (same algebra, 11 instead of
@@ -23,7 +24,7 @@
 //     forward's, bit for bit (an alpha next to the 1/255 threshold is redone with the forward's expf).
 // Sum order and roundings differ from the reference's atomics -> gradients are compared with a tolerance
 // (measured on C2 against the reference CUDA: the same distance as two runs of the reference from each other,
-// tools/grad_ratio.py).  Bound: FP32 issue.
+// tools/grad_ratio.py).  Bound: warp-instruction issue (82 %) and the L1TEX data pipe (69 % of its wavefront rate).
 #include "blend_common.cuh"
 
 namespace gsr {

@@ -517,9 +517,12 @@ def run_gsr(args):
         return
     top = max(stages, key=lambda k: stages[k]["ms"])
     t = stages[top]
-    traffic = None  # dram bytes / launch of the dominant kernel from the committed ncu --set full capture
+    traffic, ncu = None, None  # of the dominant kernel, per launch, from the committed ncu --set full capture
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))[top]["dram_bytes_per_launch"]
+        cap = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))[top]
+        traffic = cap["dram_bytes_per_launch"]
+        ncu = {k: cap[k] for k in ("issue_active_pct", "l1tex_data_pipe_wavefronts_pct", "warp_inst_executed_per_launch")
+               if k in cap}
     except Exception:
         pass
     if t["bound"] == "hbm":
@@ -530,7 +533,12 @@ def run_gsr(args):
         roofline = {"kernel": top, "bound": "fp32-issue", "achieved": t["fp32_frac"] * fp32_peak_t, "peak": fp32_peak_t,
                     "unit": "T lane-instr/s", "frac": t["fp32_frac"], "traffic": traffic,
                     "hbm_view": {"achieved": t["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": t["hbm_frac"]},
-                    "peak_source": "148 SM x 128 FP32 lanes x sm_max_mhz; HBM " + peak_src}
+                    "peak_source": "148 SM x 128 FP32 lanes x sm_max_mhz; HBM " + peak_src,
+                    "note": "achieved = SURVEY 8(d) algorithmic lane-instructions of the REFERENCE algorithm (sum n_contrib x 20 fwd / "
+                            "45 bwd) / measured time; per-warp culling and the one-scalar backward recurrence execute fewer, so "
+                            "frac can exceed 1. What the kernel itself saturates is in `ncu` (issue slots, L1TEX data pipe)."}
+        if ncu:
+            roofline["ncu"] = ncu
     c = wl.scene["cam"]
     line = {
         "metric": metric_name(wl.P, wl.W, wl.H), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

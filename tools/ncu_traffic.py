@@ -15,9 +15,14 @@ for r in rows[2:]:
     for k, st in STAGE.items():
         if k in r[ki]:
             f = lambda i: float(r[i].replace(",", "")) * scale.get(U[i], 1.0)
-            acc[st].append((f(ri) + f(wi), float(r[ti].replace(",", ""))))
-res = {st: {"dram_bytes_per_launch": sum(b for b, _ in v) / len(v), "launches": len(v),
-            "avg_us_under_ncu": sum(t for _, t in v) / len(v)} for st, v in acc.items()}
+            g = lambda name: float(r[H.index(name)].replace(",", "")) if name in H and r[H.index(name)] else None
+            acc[st].append((f(ri) + f(wi), float(r[ti].replace(",", "")), g("smsp__inst_executed.sum"),
+                            g("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                            g("l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed")))
+avg = lambda v, i: (sum(x[i] for x in v if x[i] is not None) / max(1, sum(1 for x in v if x[i] is not None)))
+res = {st: {"dram_bytes_per_launch": avg(v, 0), "launches": len(v), "avg_us_under_ncu": avg(v, 1),
+            "warp_inst_executed_per_launch": avg(v, 2), "issue_active_pct": round(avg(v, 3), 1),
+            "l1tex_data_pipe_wavefronts_pct": round(avg(v, 4), 1)} for st, v in acc.items()}
 res["_source"] = rep.split("/")[-1] + " (ncu --set full --clock-control none, bench.py --steps 1 --views 2, C2)"
 json.dump(res, open(out, "w"), indent=1)
 print(json.dumps(res, indent=1))
