@@ -189,6 +189,14 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
     int radius = 0;
     ushort4 rect = make_ushort4(0, 0, 0, 0);
     const float px = in.means3D[3 * idx], py = in.means3D[3 * idx + 1], pz = in.means3D[3 * idx + 2];
+    // the small per-Gaussian reads are issued together with the mean (one DRAM latency instead of two)
+    float3 s_in = make_float3(0.f, 0.f, 0.f);
+    float4 q_in = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!in.cov3D_precomp) {
+      s_in = make_float3(in.scales[3 * idx], in.scales[3 * idx + 1], in.scales[3 * idx + 2]);
+      q_in = reinterpret_cast<const float4*>(in.rotations)[idx];
+    }
+    const float op_in = in.opacities[idx];
     const float depth = affine_row(cam.view, 2, px, py, pz);
     if (depth > 0.2f) {
       const float hx = affine_row(cam.proj, 0, px, py, pz);
@@ -201,8 +209,8 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
 #pragma unroll
         for (int k = 0; k < 6; k++) c3[k] = in.cov3D_precomp[6 * (size_t)idx + k];
       } else {
-        float3 s = make_float3(in.scales[3 * idx], in.scales[3 * idx + 1], in.scales[3 * idx + 2]);
-        float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
+        float3 s = s_in;
+        float4 q = q_in;
         if (EXT && in.raw_params) {  // exp / normalize activations applied here (scene/gaussian_model.py:97-105)
           s = make_float3(expf(s.x), expf(s.y), expf(s.z));
           q = act_normalize(q, nullptr);
@@ -269,7 +277,7 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
             const float* sp = in.shs + (size_t)idx * in.M * 3;
             sh_to_rgb(in.D, px, py, pz, cam.campos, [&](int i) { return __ldg(sp + i); }, rgb, cbits);
           }
-          const float op = (EXT && in.raw_params) ? act_sigmoid(in.opacities[idx]) : in.opacities[idx];
+          const float op = (EXT && in.raw_params) ? act_sigmoid(op_in) : op_in;
           g.depths[idx] = depth;
           g.means2D[idx] = make_float2(pix_x, pix_y);
           g.conic_opacity[idx] = make_float4(mul(cov.z, det_inv), mul(det_inv, -cov.y), mul(cov.x, det_inv), op);
