@@ -190,7 +190,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     __syncthreads();
     if (done_cnt + tid < n_live) {
       const uint32_t g = point_list[range.x + (n_live - 1 - done_cnt - tid)];
-      stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr);
+      stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr, (float)(blockIdx.x * TILE_X), (float)(blockIdx.y * TILE_Y));
       M.id[tid] = g;
     }
     __syncthreads();

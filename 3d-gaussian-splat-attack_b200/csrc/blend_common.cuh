@@ -39,18 +39,27 @@ __device__ __forceinline__ float gauss_power(float dx, float dy, float A, float 
 // One staged list entry (shared memory, SoA of vector words).
 struct BlendStage {
   float4 a[BLEND_BATCH];  // x, y, conic A, conic B
-  float4 b[BLEND_BATCH];  // conic C, power threshold, -B/C, -B/A   (a and b are all the rectangle cull reads)
+  float4 b[BLEND_BATCH];  // conic C, cull threshold (see stage_entry), -B/C, -B/A   (a and b are all the cull reads)
   float4 c[BLEND_BATCH];  // opacity, r, g, b
 };
 
+// (tx0, ty0) = the tile's first pixel.  The rounding margin of the rectangle cull and its "not safely positive
+// definite" escape depend on the entry and the tile only, so the staging thread folds them into the threshold once
+// for all eight warps: thr_cull = thr - (2e-6 * S_tile + 1e-4), or -inf for a degenerate conic (never culled);
+// S_tile bounds the term magnitudes over the whole tile, hence over every warp rectangle.
 __device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g, const float2* __restrict__ means2D,
                                             const float4* __restrict__ conic_opacity,
-                                            const float4* __restrict__ rgb_thr) {
+                                            const float4* __restrict__ rgb_thr, float tx0, float ty0) {
   const float2 xy = means2D[g];
   const float4 co = conic_opacity[g];
   const float4 ct = rgb_thr[g];
+  const float ux = tx0 - xy.x, vy = ty0 - xy.y;
+  const float um = fmaxf(fabsf(ux), fabsf(ux + (float)(TILE_X - 1))), vm = fmaxf(fabsf(vy), fabsf(vy + (float)(TILE_Y - 1)));
+  const float s_tile = 0.5f * (co.x * um * um + co.z * vm * vm) + fabsf(co.y) * um * vm;
+  const bool degenerate = !(co.y * co.y < 0.99999f * (co.x * co.z));
+  const float thr_cull = degenerate ? -INFINITY : ct.w - (2e-6f * s_tile + 1e-4f);
   S.a[slot] = make_float4(xy.x, xy.y, co.x, co.y);
-  S.b[slot] = make_float4(co.z, ct.w, __fdividef(-co.y, co.z), __fdividef(-co.y, co.x));
+  S.b[slot] = make_float4(co.z, thr_cull, __fdividef(-co.y, co.z), __fdividef(-co.y, co.x));
   S.c[slot] = make_float4(co.w, ct.x, ct.y, ct.z);
 }
 
@@ -72,10 +81,7 @@ __device__ __forceinline__ bool rect_may_contribute(const float4 a, const float4
   const float u2 = fminf(fmaxf(b.w * v2, ux0), ux1);
   const float f1 = -0.5f * (A * u1 * u1 + C * v1 * v1) - B * u1 * v1;
   const float f2 = -0.5f * (A * u2 * u2 + C * v2 * v2) - B * u2 * v2;
-  const float um = fmaxf(fabsf(ux0), fabsf(ux1)), vm = fmaxf(fabsf(vy0), fabsf(vy1));
-  const float smax = 0.5f * (A * um * um + C * vm * vm) + fabsf(B) * um * vm;
-  const bool degenerate = !(B * B < 0.99999f * (A * C));  // not safely positive definite: do not cull
-  return degenerate || !(fmaxf(f1, f2) + 2e-6f * smax + 1e-4f < thr);
+  return !(fmaxf(f1, f2) < thr);  // thr carries the margin and the degenerate-conic escape (stage_entry)
 }
 
 }  // namespace gsr

@@ -50,7 +50,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     if (__syncthreads_count(done) == TILE_PIX) break;
     if (base + tid < range.y) {
       const uint32_t g = point_list[base + tid];
-      stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr);
+      stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr, (float)(blockIdx.x * TILE_X), (float)(blockIdx.y * TILE_Y));
       if (K > 0) s_id[tid] = g;
     }
     __syncthreads();
