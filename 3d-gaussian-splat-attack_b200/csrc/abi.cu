@@ -40,6 +40,8 @@ void profile_end(int stage, cudaStream_t st) {
   g_prof_n++;
 }
 
+static inline bool misaligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; }
+
 static int check_inputs(const gsr_inputs* in) {
   if (!in) { set_error("inputs is NULL"); return GSR_ERR_INVALID; }
   if (in->P < 0 || in->W <= 0 || in->H <= 0) { set_error("bad sizes P=%d W=%d H=%d", in->P, in->W, in->H); return GSR_ERR_INVALID; }
@@ -61,6 +63,10 @@ static int check_inputs(const gsr_inputs* in) {
   if (in->shs_rest && (!in->shs || in->M < 2)) { set_error("shs_rest needs shs (the DC block) and M >= 2"); return GSR_ERR_INVALID; }
   if (in->raw_params != 0 && in->raw_params != 1) { set_error("raw_params must be 0 or 1"); return GSR_ERR_INVALID; }
   if (in->K != 0 && (in->K != MAX_OBJ || !in->obj_feats)) { set_error("object channels: K must be 0 or 16 with obj_feats"); return GSR_ERR_INVALID; }
+  // arrays the kernels move with 16-byte accesses (include/gsr_b200.h: "device pointers are 16-byte aligned")
+  if (misaligned16(in->shs) || misaligned16(in->rotations) || misaligned16(in->obj_feats)) {
+    set_error("shs, rotations and obj_feats must be 16-byte aligned"); return GSR_ERR_INVALID;
+  }
   return GSR_OK;
 }
 
@@ -240,6 +246,9 @@ static int backward_impl(const gsr_inputs* in, const void* geom, const int32_t* 
   if (in->colors_precomp && !dL_dcolor) { set_error("dL_dcolor NULL but colors_precomp given"); return GSR_ERR_INVALID; }
   if (in->K > 0 && (!dL_dobjpix || !dL_dobj)) { set_error("object gradients NULL but K>0"); return GSR_ERR_INVALID; }
   if (accumulate && in->K > 0) { set_error("backward_accumulate: object channels are not supported"); return GSR_ERR_INVALID; }
+  if (misaligned16(dL_dsh) || misaligned16(dL_drot) || misaligned16(dL_dobj) || misaligned16(scratch)) {
+    set_error("dL_dsh, dL_drot, dL_dobj and scratch must be 16-byte aligned (vector stores / reductions)"); return GSR_ERR_INVALID;
+  }
   if (scratch_bytes < Scratch(nullptr, in->P, 0).bytes) { set_error("scratch too small"); return GSR_ERR_CAPACITY; }
   Geom g(const_cast<void*>(geom), in->P);
   Image im(const_cast<void*>(image), in->W, in->H);

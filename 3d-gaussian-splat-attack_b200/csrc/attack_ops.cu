@@ -31,7 +31,9 @@ __device__ __forceinline__ float linf_one(float p, float g, float p0, float alph
 __global__ void __launch_bounds__(EW_THREADS)
 pgd_linf_kernel(float* __restrict__ p, const float* __restrict__ g, const float* __restrict__ p0, int64_t n,
                 float alpha, float eps) {
-  const int64_t n4 = n >> 2, stride = (int64_t)gridDim.x * blockDim.x;
+  // 16-byte accesses only when all three pointers allow them (slices of a flat buffer may start anywhere)
+  const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(p0)) & 15) == 0;
+  const int64_t n4 = vec ? n >> 2 : 0, stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 a = reinterpret_cast<float4*>(p)[i];
     const float4 b = reinterpret_cast<const float4*>(g)[i], c = reinterpret_cast<const float4*>(p0)[i];

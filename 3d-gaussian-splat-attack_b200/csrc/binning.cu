@@ -111,6 +111,7 @@ duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t*
                        const uint32_t* __restrict__ tiles_touched, const ushort4* __restrict__ rects, int gx,
                        uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ hist,
                        uint32_t mask1) {
+  // mask1 <= 255 whenever hist != nullptr (end_bit <= 16, launch_duplicate_tiles): sh[] has two 256-bin rows
   __shared__ uint32_t sh[2 * 256];
   for (int k = threadIdx.x; k < 2 * 256; k += DUP_THREADS) sh[k] = 0;
   __syncthreads();
@@ -134,8 +135,10 @@ duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t*
         const uint32_t key = (y0 + y) * gx + x0 + x;
         keys[off + t] = key;
         vals[off + t] = id;
-        atomicAdd(&sh[key & 255u], 1u);
-        atomicAdd(&sh[256 + ((key >> 8) & mask1)], 1u);
+        if (hist) {
+          atomicAdd(&sh[key & 255u], 1u);
+          atomicAdd(&sh[256 + ((key >> 8) & mask1)], 1u);
+        }
         if (++x == w) { x = 0; y++; }
       }
     }
@@ -151,8 +154,10 @@ duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t*
         const uint32_t key = (by + y) * gx + bx + x;
         keys[o + t] = key;
         vals[o + t] = bid;
-        atomicAdd(&sh[key & 255u], 1u);
-        atomicAdd(&sh[256 + ((key >> 8) & mask1)], 1u);
+        if (hist) {
+          atomicAdd(&sh[key & 255u], 1u);
+          atomicAdd(&sh[256 + ((key >> 8) & mask1)], 1u);
+        }
       }
     }
   }

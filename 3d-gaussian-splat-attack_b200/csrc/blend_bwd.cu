@@ -143,7 +143,7 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
 }
 
 template <int K>
-__global__ void __launch_bounds__(TILE_PIX, (K > 0 ? 1 : GSR_BWD_MINBLOCKS))
+__global__ void __launch_bounds__(TILE_PIX, (K > 0 ? 2 : GSR_BWD_MINBLOCKS))
 blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                  const float* __restrict__ bg, const float2* __restrict__ means2D,
                  const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb_thr,
@@ -153,6 +153,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BwdSmem& M = *reinterpret_cast<BwdSmem*>(smem_raw);
   BlendStage& S = M.S;
+  // K = 16: the staged entries' object features, four 16-byte words per entry, behind BwdSmem
+  float4 (*s_obj)[BLEND_BATCH] = reinterpret_cast<float4 (*)[BLEND_BATCH]>(smem_raw + sizeof(BwdSmem));
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   BwdWarp& Wp = M.w[warp];
@@ -192,6 +194,11 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       const uint32_t g = point_list[range.x + (n_live - 1 - done_cnt - tid)];
       stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr, (float)(blockIdx.x * TILE_X), (float)(blockIdx.y * TILE_Y));
       M.id[tid] = g;
+      if (K > 0) {
+        const float4* f = reinterpret_cast<const float4*>(obj_feats + (size_t)g * K);
+#pragma unroll
+        for (int q = 0; q < K / 4; q++) s_obj[q][tid] = __ldg(f + q);
+      }
     }
     __syncthreads();
     const int nb = (int)min((uint32_t)BLEND_BATCH, n_live - done_cnt);
@@ -266,12 +273,14 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           T = T * inv;
           wc = alpha * T;
           if (K > 0) {
-            const float* f = obj_feats + (size_t)M.id[j] * K;
 #pragma unroll
-            for (int k = 0; k < K; k++) {
-              cd = fmaf(__ldg(f + k), dpo[k], cd);
-              vo[k] = wc * dpo[k];
+            for (int q = 0; q < K / 4; q++) {
+              const float4 f = s_obj[q][j];
+              cd = fmaf(f.x, dpo[4 * q], cd); cd = fmaf(f.y, dpo[4 * q + 1], cd);
+              cd = fmaf(f.z, dpo[4 * q + 2], cd); cd = fmaf(f.w, dpo[4 * q + 3], cd);
             }
+#pragma unroll
+            for (int k = 0; k < K; k++) vo[k] = wc * dpo[k];
           }
           const float dL_dalpha = fmaf(T, cd, -behind * inv);
           behind = fmaf(cd, wc, behind);
@@ -306,9 +315,14 @@ int launch_blend_bwd(const gsr_inputs& in, const Geom& g, const Image& im, const
   if (in.K > 0) GSR_CUDA_CHECK(cudaMemsetAsync(dL_dobj, 0, (size_t)in.P * in.K * sizeof(float), st));
 #define GSR_BLEND_BWD(KK)                                                                                       \
   do {                                                                                                          \
-    GSR_CUDA_CHECK(cudaFuncSetAttribute(blend_bwd_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
-                                        (int)sizeof(BwdSmem)));                                                 \
-    blend_bwd_kernel<KK><<<grid, block, sizeof(BwdSmem), st>>>(im.ranges, point_list, in.W, in.H, in.bg,        \
+    constexpr size_t smem = sizeof(BwdSmem) + (size_t)KK * BLEND_BATCH * sizeof(float);                         \
+    static bool attr_set = false;                                                                               \
+    if (!attr_set) {                                                                                            \
+      GSR_CUDA_CHECK(cudaFuncSetAttribute(blend_bwd_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize,    \
+                                          (int)smem));                                                          \
+      attr_set = true;                                                                                          \
+    }                                                                                                           \
+    blend_bwd_kernel<KK><<<grid, block, smem, st>>>(im.ranges, point_list, in.W, in.H, in.bg,                   \
                                                                g.means2D, g.conic_opacity, g.rgb_thr,           \
                                                                in.obj_feats, im.final_T, im.n_contrib, dL_dpix, \
                                                                dL_dobjpix, accum, dL_dobj);                     \

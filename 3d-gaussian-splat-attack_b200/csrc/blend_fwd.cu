@@ -27,7 +27,9 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                  float* __restrict__ out_color, float* __restrict__ out_objects) {
   __shared__ BlendStage S;
-  __shared__ uint32_t s_id[K > 0 ? BLEND_BATCH : 1];
+  // object-identity features of the staged entries, four 16-byte words per entry (K = 16): staged with the batch, so
+  // the blending loop reads them as broadcast shared loads instead of 16 global loads per contributing pair
+  __shared__ float4 s_obj[K > 0 ? K / 4 : 1][K > 0 ? BLEND_BATCH : 1];
   __shared__ uint8_t s_q[TILE_PIX / 32][32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -51,7 +53,11 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     if (base + tid < range.y) {
       const uint32_t g = point_list[base + tid];
       stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr, (float)(blockIdx.x * TILE_X), (float)(blockIdx.y * TILE_Y));
-      if (K > 0) s_id[tid] = g;
+      if (K > 0) {
+        const float4* f = reinterpret_cast<const float4*>(obj_feats + (size_t)g * K);
+#pragma unroll
+        for (int q = 0; q < K / 4; q++) s_obj[q][tid] = __ldg(f + q);
+      }
     }
     __syncthreads();
     const int nb = min(BLEND_BATCH, todo);
@@ -80,6 +86,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         // (forward.cu:336-349) become predicates on the accumulation -- same values, same decisions, no divergent
         // region in the loop (the per-Gaussian threshold pre-test is left to the rectangle cull).
         const float4 c = S.c[j];
+        float wobj = 0.f;  // alpha * T of this pair when it contributes (object channels only)
         const bool p1 = !done && !(power > 0.0f);
         const float alpha = fminf(0.99f, fpx::mul(c.x, expf(power)));
         const bool p2 = p1 && !(alpha < 1.0f / 255.0f);
@@ -90,18 +97,24 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           C0 = fpx::fma_(T, fpx::mul(alpha, c.y), C0);
           C1 = fpx::fma_(T, fpx::mul(alpha, c.z), C1);
           C2 = fpx::fma_(T, fpx::mul(alpha, c.w), C2);
-          if (K > 0) {
-            const float* f = obj_feats + (size_t)s_id[j] * K;
-#pragma unroll
-            for (int k = 0; k < K; k++) O[k] = fpx::fma_(T, fpx::mul(alpha, __ldg(f + k)), O[k]);
-          }
+          if (K > 0) wobj = T * alpha;
           T = test_T;
           last_contributor = first + j + 1;
 #ifdef GSR_STATS
           atomicAdd(&g_blend_stats[4], 1ull);
 #endif
         }
+        if (K > 0 && __any_sync(0xffffffffu, wobj != 0.f)) {
+          // O_k += f_k * alpha * T (Gaussian-Grouping's extra channels: same weights as the colour, no background)
+#pragma unroll
+          for (int q = 0; q < K / 4; q++) {
+            const float4 f = s_obj[q][j];
+            O[4 * q] = fmaf(wobj, f.x, O[4 * q]); O[4 * q + 1] = fmaf(wobj, f.y, O[4 * q + 1]);
+            O[4 * q + 2] = fmaf(wobj, f.z, O[4 * q + 2]); O[4 * q + 3] = fmaf(wobj, f.w, O[4 * q + 3]);
+          }
+        }
       }
+      __syncwarp();  // the queue is rewritten next round: votes and shuffles are not memory barriers
     }
   }
   if (inside) {

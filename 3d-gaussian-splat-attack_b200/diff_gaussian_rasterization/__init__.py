@@ -32,7 +32,9 @@ def cpu_deep_copy_tuple(input_tuple):
 
 
 class _DeviceState:
-    """Per-device reusable scratch (stream-ordered reuse), pinned read-back word."""
+    """Reusable scratch and pinned read-back word of one (device, stream): calls issued on different streams of a
+    device (or from different host threads using different streams) never share sort buffers, backward
+    accumulators or the duplicate-count word (the reference allocates these per call)."""
 
     def __init__(self, device):
         self.device = device
@@ -51,10 +53,11 @@ _states = {}
 
 
 def _state(device):
-    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    key = (index, torch.cuda.current_stream(index).cuda_stream)
     st = _states.get(key)
     if st is None:
-        st = _states[key] = _DeviceState(torch.device("cuda", key[1]))
+        st = _states[key] = _DeviceState(torch.device("cuda", index))
     return st
 
 
@@ -69,7 +72,10 @@ def _f32c(t, name):
         raise RuntimeError(f"{name} must be a CUDA tensor (this rasterizer has no CPU path)")
     if t.dtype != torch.float32:
         t = t.float()
-    return t.contiguous()
+    t = t.contiguous()
+    if t.data_ptr() & 15:  # a view into a packed buffer: the kernels move shs / rotations / sh_objs as 16-byte words
+        t = t.clone()
+    return t
 
 
 def _make_inputs(rs, P, M, K, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, sh_objs, keep,
@@ -177,10 +183,14 @@ class _RasterizeGaussians(torch.autograd.Function):
                 print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
             raise ex
 
+        # undefined output gradients arrive as None instead of zero tensors: a loss that never reads
+        # `rendered_objects` (attack.py:485-494 uses render_pkg["render"] only) then runs the K = 0 backward
+        ctx.set_materialize_grads(False)
         ctx.raster_settings = rs
         ctx.num_rendered = L
         ctx.dims = (P, M, K if want_obj else 0)
         ctx.want_obj = want_obj
+        ctx.obj_shape = tuple(sh_objs.shape) if want_obj else None
         ctx.dev = dev
         empty = torch.empty(0, device=dev)
         ctx.save_for_backward(*[t if t is not None else empty for t in
@@ -199,8 +209,12 @@ class _RasterizeGaussians(torch.autograd.Function):
             [t if t.numel() else None for t in ctx.saved_tensors]
         dev = ctx.dev
         H, W = int(rs.image_height), int(rs.image_width)
+        if grad_out_color is None and grad_out_objects is None:
+            return (None,) * 10
         if grad_out_color is None:
             grad_out_color = torch.zeros((3, H, W), dtype=torch.float32, device=dev)
+        if grad_out_objects is None:  # no gradient reaches the object channels: colour-only backward
+            K, obj_c = 0, None
 
         def new(*shape):
             return torch.empty(shape, dtype=torch.float32, device=dev)
@@ -214,10 +228,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         g_obj = new(P, K) if K else None
         if P:
             dpix = _f32c(grad_out_color, "grad_out_color")
-            dobj = None
-            if K:
-                dobj = _f32c(grad_out_objects, "grad_out_objects") if grad_out_objects is not None else \
-                    torch.zeros((K, H, W), dtype=torch.float32, device=dev)
+            dobj = _f32c(grad_out_objects, "grad_out_objects") if K else None
             debug_args = None
             if rs.debug:  # reference _C backward argument order (__init__.py:109-139)
                 debug_args = cpu_deep_copy_tuple((rs.bg, means3D_c, radii, col_c, sc_c, rot_c, rs.scale_modifier, cov_c,
@@ -243,8 +254,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                     torch.save(debug_args, "snapshot_bw.dump")
                     print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
-        if g_obj is not None and obj_c is not None:
-            g_obj = g_obj.view(obj_c.shape)
+        if g_obj is not None:
+            g_obj = g_obj.view(ctx.obj_shape)
         # same order as the forward inputs (reference __init__.py:143-153), sh_objs appended
         return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov, None, g_obj)
 

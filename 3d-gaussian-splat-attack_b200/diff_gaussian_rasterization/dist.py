@@ -12,7 +12,7 @@ from typing import Callable, Dict, Iterable, List, Optional, Sequence
 import torch
 import torch.distributed as dist
 
-__all__ = ["shard_views", "FlatGradBucket", "sharded_step", "sharded_accumulate_step", "backprop_inputs"]
+__all__ = ["shard_views", "flat_layout", "FLAT_ALIGN", "FlatGradBucket", "sharded_step", "sharded_accumulate_step", "backprop_inputs"]
 
 
 def shard_views(n_views: int, rank: int, world: int) -> List[int]:
@@ -23,8 +23,23 @@ def shard_views(n_views: int, rank: int, world: int) -> List[int]:
     return list(range(rank, n_views, world))
 
 
+FLAT_ALIGN = 64  # elements: every slice of a flat buffer starts on a 256-byte boundary (include/gsr_b200.h)
+
+
+def flat_layout(sizes: Dict[str, int], align: int = FLAT_ALIGN):
+    """Offsets of named slices inside one flat buffer, each slice start rounded up to `align` elements, so that a
+    slice handed to the kernels (16-byte vector loads / reductions on shs, rotations and their gradients) is aligned
+    for ANY Gaussian count.  Returns ({name: (begin, end)}, total elements)."""
+    slices, off = {}, 0
+    for n, k in sizes.items():
+        off = (off + align - 1) // align * align
+        slices[n] = (off, off + int(k))
+        off += int(k)
+    return slices, (off + align - 1) // align * align
+
+
 class FlatGradBucket:
-    """One flat fp32 gradient buffer shared by all attribute tensors.
+    """One flat fp32 gradient buffer shared by all attribute tensors (slices 256-byte aligned, see flat_layout).
 
     `params` maps names to leaf tensors (xyz, SH, scale, rotation, opacity ...).  After construction each
     p.grad is a view into `self.flat`, so autograd accumulates per-view gradients straight into the bucket
@@ -45,15 +60,12 @@ class FlatGradBucket:
             if p.device != dev or p.dtype != dt:
                 raise ValueError(f"{n}: all parameters must share device and dtype")
         self.params = dict(params)
-        self.numel = sum(p.numel() for p in ps)
-        self.flat = torch.zeros(self.numel, dtype=dt, device=dev)
-        self.slices = {}
-        off = 0
-        for n, p in self.params.items():
-            self.slices[n] = (off, off + p.numel())
-            if bind:
-                p.grad = self.flat[off:off + p.numel()].view(p.shape)
-            off += p.numel()
+        self.slices, self.numel = flat_layout({n: p.numel() for n, p in self.params.items()})
+        self.flat = torch.zeros(self.numel, dtype=dt, device=dev)  # padding stays zero: harmless in the all-reduce
+        if bind:
+            for n, p in self.params.items():
+                a, b = self.slices[n]
+                p.grad = self.flat[a:b].view(p.shape)
 
     def zero(self):
         self.flat.zero_()

@@ -3,7 +3,8 @@
 A step = render `n_views` cameras forward + backward against one Gaussian set and return the summed
 attribute gradients (the inner loop of attack.py:463-530 with the detector replaced by a given dL/dimage).
 Inputs per step (pinned host memory): the flat attribute vector [means3D | shs | scales | rotations | opacities]
-(236 B per Gaussian at SH degree 3 -- the same layout as the all-reduce bucket, dist.FlatGradBucket), one
+(236 B per Gaussian at SH degree 3; each slice starts on a 256-byte boundary, `HostStepPipeline.slices`, see
+dist.flat_layout -- the same layout as the all-reduce bucket, dist.FlatGradBucket), one
 36-float row per camera (viewmatrix 16, projmatrix 16, campos 3, pad) and one (3,H,W) dL/dimage per camera.
 Output per step: the flat gradient vector in pinned host memory.
 
@@ -19,6 +20,7 @@ import torch
 
 from . import GaussianRasterizationSettings
 from . import views as _views
+from .dist import flat_layout
 
 __all__ = ["HostStepPipeline", "ATTRS", "bind_host_to_gpu_numa"]
 
@@ -56,12 +58,13 @@ class _Slot:
         self.grad = torch.zeros(n_param, dtype=f32, device=dev)
         self.cam = torch.empty((n_views, 36), dtype=f32, device=dev)
         self.dL = torch.empty((n_views, 3, H, W), dtype=f32, device=dev)
-        self.p, self.g, off = {}, {}, 0
+        self.p, self.g = {}, {}
+        slices, _ = flat_layout({n: P * w for n, w in widths})
         for n, w in widths:
             shape = (P, w // 3, 3) if n == "shs" else (P, w)
-            self.p[n] = self.param[off:off + P * w].view(shape)
-            self.g[n] = self.grad[off:off + P * w].view(shape)
-            off += P * w
+            a, b = slices[n]
+            self.p[n] = self.param[a:b].view(shape)
+            self.g[n] = self.grad[a:b].view(shape)
         self.ev_in = torch.cuda.Event()
         self.ev_compute = torch.cuda.Event()
         self.ev_out = torch.cuda.Event()
@@ -79,7 +82,8 @@ class HostStepPipeline:
         self.tanfovx, self.tanfovy, self.sh_degree = float(tanfovx), float(tanfovy), int(sh_degree)
         self.dev = torch.device(device)
         self.widths = (("means3D", 3), ("shs", 3 * M), ("scales", 3), ("rotations", 4), ("opacities", 1))
-        self.n_param = P * sum(w for _, w in self.widths)
+        # host and device share one layout: slices[name] = (begin, end) in floats, every begin 256-byte aligned
+        self.slices, self.n_param = flat_layout({n: P * w for n, w in self.widths})
         self.bg = torch.zeros(3, device=self.dev) if bg is None else bg.to(self.dev).float()
         self.slots: List[_Slot] = [_Slot(self.n_param, n_views, H, W, self.dev, self.widths, P) for _ in range(depth)]
         self.s_in = torch.cuda.Stream(self.dev)

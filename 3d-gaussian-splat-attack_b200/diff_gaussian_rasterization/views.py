@@ -73,6 +73,13 @@ def forward_view(raster_settings, means3D, opacities, shs=None, colors_precomp=N
     return color, radii, ViewState(raster_settings, P, M, L, t, radii, geom, point_list, image, bool(raw_params))
 
 
+def _check_aligned(name, g):
+    """shs / rotations gradients are accumulated with 16-byte vector reductions (include/gsr_b200.h)."""
+    if name in ("shs", "rotations") and g.data_ptr() & 15:
+        raise RuntimeError(f"grads['{name}'] must be 16-byte aligned: lay flat buffers out with dist.flat_layout "
+                           "(FlatGradBucket does)")
+
+
 def _sh_count(shs, shs_rest):
     """Total SH coefficients M from either layout: shs (P,M,3), or shs (P,1,3) + shs_rest (P,M-1,3)."""
     if shs is None:
@@ -107,6 +114,7 @@ def backward_view(state: ViewState, dL_dimage: torch.Tensor, grads: Dict[str, Op
             return None
         if not g.is_cuda or g.dtype != torch.float32 or not g.is_contiguous() or g.numel() != shape_numel:
             raise RuntimeError(f"grads['{name}'] must be a contiguous float32 CUDA tensor with {shape_numel} elements")
+        _check_aligned(name, g)
         return g
 
     g_m3 = buf("means3D", True, P * 3)
@@ -313,7 +321,17 @@ class ViewPipeline:
                 if gbuf is not None and (not gbuf.is_cuda or gbuf.dtype != torch.float32 or not gbuf.is_contiguous()
                                          or (need and gbuf.numel() != t[name].numel())):
                     raise RuntimeError(f"grads['{name}'] must be a contiguous float32 CUDA tensor shaped like the input")
+                if gbuf is not None:
+                    _check_aligned(name, gbuf)
             R = torch.cuda.current_stream(self.dev)
+            # Camera tensors of EVERY view are brought to contiguous float32 device memory here, on the caller's
+            # stream and before ev_start: Camera.world_view_transform is a transposed (non-contiguous) CUDA tensor
+            # (scene/cameras.py:54), so .contiguous() launches a copy that the G and B streams must not overtake.
+            # The list keeps them alive until the end of the step, where R has waited for G and B.
+            settings = [rs._replace(bg=_f32c(rs.bg.to(self.dev), "bg"),
+                                    viewmatrix=_f32c(rs.viewmatrix.to(self.dev), "viewmatrix"),
+                                    projmatrix=_f32c(rs.projmatrix.to(self.dev), "projmatrix"),
+                                    campos=_f32c(rs.campos.to(self.dev), "campos")) for rs in settings]
             if self.overlap:  # whatever produced the inputs on the caller's stream must be visible to G
                 self.ev_start.record(R)
                 self.G.wait_event(self.ev_start)

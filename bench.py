@@ -56,10 +56,14 @@ def parse_args():
     ap.add_argument("--P", type=int, default=None, help="override Gaussian count (debug)")
     ap.add_argument("--api", default="views", choices=["views", "autograd"],
                     help="views: forward_view/backward_view accumulate API; autograd: drop-in GaussianRasterizer")
+    ap.add_argument("--sh-objs", action="store_true",
+                    help="with --api autograd: pass sh_objs (P,1,16) and build the screen-space tensor per call, exactly as "
+                         "the reference's gaussian_renderer.render() does (gaussian_renderer/__init__.py:26,81-95)")
     ap.add_argument("--no-overlap", action="store_true",
                     help="views API without the two-stream ViewPipeline (everything on one stream)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-drop-in", action="store_true", help="skip the drop-in autograd API measurements")
     ap.add_argument("--cpu-sample-views", type=int, default=1)
     ap.add_argument("--stages-out", default=None, help="write the per-stage table as JSON to this file")
     return ap.parse_args()
@@ -202,16 +206,18 @@ class Workload:
         sc = self.scene = make_scene(args.workload, P=args.P)
         self.P, self.W, self.H = sc["P"], sc["cam"]["image_width"], sc["cam"]["image_height"]
         self.cams = cameras_for(sc, args.views * world)[rank::world]
-        host = np.concatenate([sc[n].reshape(-1) for n, _ in ATTRS]).astype(np.float32)
+        from diff_gaussian_rasterization.dist import FlatGradBucket, flat_layout
+        slices, n_flat = flat_layout({n: self.P * k for n, k in ATTRS})  # every slice 256-byte aligned for any P
+        host = np.zeros(n_flat, np.float32)
+        for n, _ in ATTRS:
+            host[slices[n][0]:slices[n][1]] = sc[n].reshape(-1)
         self.host_param = torch.from_numpy(host).pin_memory()
         self.host_grad = torch.empty_like(self.host_param).pin_memory()
         self.flat_param = self.host_param.to(dev)
-        from diff_gaussian_rasterization.dist import FlatGradBucket
-        self.params, off = {}, 0
+        self.params = {}
         for n, k in ATTRS:
-            sz = self.P * k
-            self.params[n] = self.flat_param[off:off + sz].view(SHAPES[n]).detach().requires_grad_(True)
-            off += sz
+            a, b = slices[n]
+            self.params[n] = self.flat_param[a:b].view(SHAPES[n]).detach().requires_grad_(True)
         self.bucket = FlatGradBucket(self.params)  # every .grad is a view into bucket.flat (the NCCL bucket)
         self.flat_grad = self.bucket.flat
         self.means2D = torch.zeros((self.P, 3), device=dev)  # dummy screen-space tensor (no grad wanted)
@@ -226,6 +232,8 @@ class Workload:
         self.dev_cam = self.host_cam.to(dev)
         self.bg = torch.zeros(3, device=dev)
         self.api = args.api
+        self.sh_objs = bool(getattr(args, "sh_objs", False))
+        self.obj = None
         self.grads = {n: self.bucket.grad(n) for n, _ in ATTRS}
         self.overlap = not args.no_overlap
         self.vp = None
@@ -252,11 +260,32 @@ class Workload:
             self.last_state, self.last_radii = st, radii
             views.backward_view(st, self.dev_dL[v], self.grads)
             return
+        if self.sh_objs:
+            self.view_render_like(v)
+            return
         color, radii = self.dgr.GaussianRasterizer(self.settings(v))(
             means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"], shs=p["shs"],
             scales=p["scales"], rotations=p["rotations"])
         self.last_fn, self.last_radii = color.grad_fn, radii
         self.torch.autograd.backward([color], [self.dev_dL[v]])
+
+    def view_render_like(self, v):
+        """What the reference's render() does around the rasterizer call (gaussian_renderer/__init__.py:26-103) on
+        pre-activated attributes: a fresh screen-space tensor with retain_grad, sh_objs always passed, the
+        visibility filter; the loss reads the colour image only (attack.py:485-494)."""
+        t, p = self.torch, self.params
+        if self.obj is None:
+            g = t.Generator(device=self.dev).manual_seed(7)
+            self.obj = t.rand((self.P, 1, 16), device=self.dev, generator=g).requires_grad_(True)
+        ssp = t.zeros_like(p["means3D"], requires_grad=True) + 0
+        ssp.retain_grad()
+        color, radii, objects = self.dgr.GaussianRasterizer(self.settings(v))(
+            means3D=p["means3D"], means2D=ssp, opacities=p["opacities"], shs=p["shs"], sh_objs=self.obj,
+            scales=p["scales"], rotations=p["rotations"])
+        pkg = {"render": color, "viewspace_points": ssp, "visibility_filter": radii > 0, "radii": radii,
+               "render_object": objects}
+        self.last_fn, self.last_radii = color.grad_fn, radii
+        t.autograd.backward([pkg["render"]], [self.dev_dL[v]])
 
     def view_fwd_only(self, v):
         p = self.params
@@ -507,6 +536,20 @@ def run_gsr(args):
                "serial": {"value": world * len(wl.cams) / (ms_s * 1e-3), "unit": UNIT, "ms_per_step": ms_s,
                           "how": "same step, copies and compute on one stream, nothing overlapped"}}
 
+    # ---- the same step through the drop-in autograd module (what gaussian_renderer.render() calls), one stream
+    drop_in = None
+    if args.api == "views" and not args.no_drop_in:
+        drop_in = {}
+        n_d = max(2, args.steps // 4)
+        for key, objs in (("autograd", False), ("autograd_sh_objs", True)):
+            wl.api, wl.sh_objs = "autograd", objs
+            ms_d = timed(torch, dist, lambda: wl.step(dist, overlap=False), n_d, 2, dev)
+            drop_in[key] = {"value": world * len(wl.cams) * n_d / (ms_d * 1e-3), "unit": UNIT, "ms_per_step": ms_d / n_d}
+        drop_in["how"] = ("GaussianRasterizer + torch autograd per view, .grad accumulation by torch, one stream; "
+                          "autograd_sh_objs passes sh_objs (16 object channels rendered, colour-only loss) and builds the "
+                          "screen-space tensor per call like gaussian_renderer.render()")
+        wl.api, wl.sh_objs = args.api, bool(args.sh_objs)
+
     # ---- per-stage timing (rank 0 reports; every rank runs it to stay in lock-step)
     stages, counts = stage_table(torch, wl, max(1, min(args.steps, 5)), hbm_peak, sm_max)
     if dist is not None:
@@ -548,7 +591,7 @@ def run_gsr(args):
                    "views_per_rank_per_step": len(wl.cams), "parallelism": f"view-sharded x{world}, replicated Gaussians"
                    + (", NCCL all-reduce of attribute gradients per step" if world > 1 else ""),
                    "l2": "inputs larger than L2 (236 MB of attributes + 25 MB dL/dpixel per view)", **counts},
-        "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "stages": stages,
+        "e2e": e2e, "drop_in": drop_in, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "stages": stages,
     }
     if not args.no_cpu_baseline and world == 1:
         steps_c = 1

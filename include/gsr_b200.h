@@ -12,7 +12,10 @@
  *  - NULL pointer = absent input (the reference passes empty tensors -> nullptr,
  *    DGR/diff_gaussian_rasterization/__init__.py:197-207, forward.cu:205,241).
  *  - The caller owns every buffer; the library never allocates device memory.  Buffer sizes come
- *    from the gsr_*_bytes() queries.  All buffers must be 256-byte aligned.
+ *    from the gsr_*_bytes() queries.  geom / image / scratch buffers must be 256-byte aligned.
+ *    Input and gradient arrays keep the reference's layouts and may start anywhere a float may,
+ *    EXCEPT the ones moved with 16-byte vector accesses: shs, rotations, obj_feats, dL_dsh,
+ *    dL_drot, dL_dobj must be 16-byte aligned (GSR_ERR_INVALID otherwise; torch allocations are).
  *  - Every launch goes to the cudaStream_t passed in (as void*); the reference uses the legacy
  *    default stream.
  *  - Every entry point returns 0 on success or a negative gsr_status; gsr_last_error() returns
