@@ -94,7 +94,7 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
   const int j = __shfl_sync(0xffffffffu, slot_j, e);
   if (e < ng) {
     const float2 cxy = *reinterpret_cast<const float2*>(&M.S.a[j]);
-    cx = cxy.x; cy = cxy.y; g = M.id[j];
+    cx = cxy.y; cy = cxy.x; g = M.id[j];  // staged as (y, x)
   }
   const float2* row = &Wp.panel[e][h * GRP];
   const float2* pix_rg = &Wp.pix_rg[h * GRP];
@@ -108,7 +108,8 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
     const float2 rg = pix_rg[i];
     const float4 dp = make_float4(rg.x, rg.y, pix_b[i], 0.f);
     const int lx = i & 7, r = i >> 3;
-    s0 = fmaf(pr.x, dp.x, s0); s1 = fmaf(pr.x, dp.y, s1); s2 = fmaf(pr.x, dp.z, s2);
+    fpx::fma2_bcast(s0, s1, dp.x, dp.y, pr.x);  // (s0, s1) += wc * (dL/dr, dL/dg): one FFMA2
+    s2 = fmaf(pr.x, dp.z, s2);
     M0 += pr.y;
     if (lx == 1) { Mx += pr.y; Mxx += pr.y; }
     if (lx > 1) { Mx = fmaf(pr.y, (float)lx, Mx); Mxx = fmaf(pr.y, (float)(lx * lx), Mxx); }
@@ -161,7 +162,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   const uint32_t wx0 = blockIdx.x * TILE_X + (warp & 1) * WARP_W, wy0 = blockIdx.y * TILE_Y + (warp >> 1) * WARP_H;
   const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-  const float pxf = (float)px, pyf = (float)py, wx0f = (float)wx0, wy0f = (float)wy0;
+  const float npxf = -(float)px, npyf = -(float)py, wx0f = (float)wx0, wy0f = (float)wy0;
   const size_t HW = (size_t)W * H, pid = (size_t)py * W + px;
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
 
@@ -215,10 +216,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         rest &= ~(0x80000000u >> lz);
         const int j = r + lz;
         const float4 a = S.a[j];
-        const float4 b = S.b[j];
         const uint32_t pos = top - j;
-        const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
-        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
+        const float power = gauss_power_packed(a, S.b[j].x, npyf, npxf);  // the forward's bits
         // (no `power < threshold` pre-test here: alpha is evaluated on every lane anyway and decides alone)
         bool hit = pos < my_last && !(power > 0.0f);
         const float4 c = S.c[j];
@@ -226,7 +225,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         float G = 0.f, alpha = 0.f;
         if (hit) {
           G = expf(power);
-          alpha = fminf(0.99f, fpx::mul(c.x, G));
+          alpha = fminf(0.99f, fpx::mul(c.w, G));
           hit = !(alpha < 1.0f / 255.0f);
         }
 #else
@@ -235,11 +234,11 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         // when some lane's alpha lands next to the 1/255 threshold (rare) the warp redoes it with the forward's
         // arithmetic.
         float G = fast_exp(power);
-        float alpha = fminf(0.99f, c.x * G);
+        float alpha = fminf(0.99f, c.w * G);
         const bool near = hit && fabsf(alpha - 1.0f / 255.0f) < 4e-8f;
         if (__any_sync(0xffffffffu, near)) {
           const float Ge = expf(fminf(power, 0.f));
-          const float ae = fminf(0.99f, fpx::mul(c.x, Ge));
+          const float ae = fminf(0.99f, fpx::mul(c.w, Ge));
           G = near ? Ge : G;
           alpha = near ? ae : alpha;
         }
@@ -257,7 +256,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           // straight-line form of the block below (no divergent region): a pair that does not contribute runs the
           // same arithmetic with alpha = 0 and G = 0, which leaves T (x 1/(1-0)) and `behind` (+ cd*0) unchanged
           const float ae = hit ? alpha : 0.f, Ge = hit ? G : 0.f;
-          const float cd = c.y * dpix[0] + c.z * dpix[1] + c.w * dpix[2];
+          const float cd = c.x * dpix[0] + c.y * dpix[1] + c.z * dpix[2];
           const float inv = fast_rcp(1.f - ae);
           T = T * inv;
           wc = ae * T;
@@ -268,7 +267,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           // dC/dalpha_j = T_j c_j - (sum_{k behind j} c_k alpha_k T_k + T_final bg) / (1 - alpha_j); dotted with
           // dL/dpixel the sum is ONE running scalar `behind` (the reference carries the same quantity per
           // channel, normalised, as accum_rec: backward.cu:499-521)
-          float cd = c.y * dpix[0] + c.z * dpix[1] + c.w * dpix[2];
+          float cd = c.x * dpix[0] + c.y * dpix[1] + c.z * dpix[2];
           const float inv = fast_rcp(1.f - alpha);
           T = T * inv;
           wc = alpha * T;

@@ -36,11 +36,25 @@ __device__ __forceinline__ float gauss_power(float dx, float dy, float A, float 
   return sub(mul(q, -0.5f), mul(dy, mul(dx, B)));
 }
 
-// One staged list entry (shared memory, SoA of vector words).
+// power from a staged record with sm_100a's packed-pair FP32 instructions: 1 FADD2 + 2 FMUL2 + FMUL + 2 FFMA instead
+// of 2 FADD + 5 FMUL + 2 FFMA, every intermediate rounded exactly as in gauss_power (same bits).  a = BlendStage::a
+// (y, x, C, B), A = BlendStage::b.x, (npy, npx) = minus the pixel centre.
+__device__ __forceinline__ float gauss_power_packed(const float4 a, float A, float npy, float npx) {
+  using namespace fpx;
+  float dy, dx, t2, t4, t3, u;
+  add2(dy, dx, a.x, a.y, npy, npx);  // (y - py, x - px)
+  mul2(t2, t4, dy, dx, a.z, a.w);    // (dy C, dx B)
+  mul2_bcast(t3, u, t2, t4, dy);     // (dy (dy C), dy (dx B))
+  const float q = fma_(dx, mul(dx, A), t3);
+  return sub(mul(q, -0.5f), u);
+}
+
+// One staged list entry (shared memory, SoA of vector words).  The order inside a word puts the operands of the
+// packed-pair instructions in even-aligned register pairs after a 16-byte shared load.
 struct BlendStage {
-  float4 a[BLEND_BATCH];  // x, y, conic A, conic B
-  float4 b[BLEND_BATCH];  // conic C, cull threshold (see stage_entry), -B/C, -B/A   (a and b are all the cull reads)
-  float4 c[BLEND_BATCH];  // opacity, r, g, b
+  float4 a[BLEND_BATCH];  // y, x, conic C, conic B
+  float4 b[BLEND_BATCH];  // conic A, cull threshold (see stage_entry), -B/C, -B/A   (a and b are all the cull reads)
+  float4 c[BLEND_BATCH];  // r, g, b, opacity
 };
 
 // (tx0, ty0) = the tile's first pixel.  The rounding margin of the rectangle cull and its "not safely positive
@@ -58,9 +72,9 @@ __device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g,
   const float s_tile = 0.5f * (co.x * um * um + co.z * vm * vm) + fabsf(co.y) * um * vm;
   const bool degenerate = !(co.y * co.y < 0.99999f * (co.x * co.z));
   const float thr_cull = degenerate ? -INFINITY : ct.w - (2e-6f * s_tile + 1e-4f);
-  S.a[slot] = make_float4(xy.x, xy.y, co.x, co.y);
-  S.b[slot] = make_float4(co.z, thr_cull, __fdividef(-co.y, co.z), __fdividef(-co.y, co.x));
-  S.c[slot] = make_float4(co.w, ct.x, ct.y, ct.z);
+  S.a[slot] = make_float4(xy.y, xy.x, co.z, co.y);
+  S.b[slot] = make_float4(co.x, thr_cull, __fdividef(-co.y, co.z), __fdividef(-co.y, co.x));
+  S.c[slot] = make_float4(ct.x, ct.y, ct.z, co.w);
 }
 
 // Conservative test of one list entry against a warp's pixel rectangle [x0, x0+WARP_W-1] x [y0, y0+WARP_H-1]:
@@ -72,9 +86,9 @@ __device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g,
 // bounded over the rectangle by Smax), so a pair that passes per pixel is never culled here.  NaNs compare
 // false and are kept.
 __device__ __forceinline__ bool rect_may_contribute(const float4 a, const float4 b, float x0, float y0) {
-  const float A = a.z, B = a.w, C = b.x, thr = b.y;
-  const float ux0 = x0 - a.x, ux1 = ux0 + (float)(WARP_W - 1);
-  const float vy0 = y0 - a.y, vy1 = vy0 + (float)(WARP_H - 1);
+  const float A = b.x, B = a.w, C = a.z, thr = b.y;
+  const float ux0 = x0 - a.y, ux1 = ux0 + (float)(WARP_W - 1);
+  const float vy0 = y0 - a.x, vy1 = vy0 + (float)(WARP_H - 1);
   const float u1 = fminf(fmaxf(0.f, ux0), ux1);
   const float v1 = fminf(fmaxf(b.z * u1, vy0), vy1);
   const float v2 = fminf(fmaxf(0.f, vy0), vy1);

@@ -19,8 +19,14 @@
 namespace gsr {
 namespace {
 
+#ifndef GSR_FWD_MINBLOCKS
+#define GSR_FWD_MINBLOCKS 6
+#endif
+#ifndef GSR_FWD_OBJ_MINBLOCKS
+#define GSR_FWD_OBJ_MINBLOCKS 4  // 64 registers; 3 blocks (79 regs) 0.589 ms, 5 blocks (48 regs, spills) 0.561 ms, 4: 0.524 ms
+#endif
 template <int K>
-__global__ void __launch_bounds__(TILE_PIX)
+__global__ void __launch_bounds__(TILE_PIX, (K > 0 ? GSR_FWD_OBJ_MINBLOCKS : GSR_FWD_MINBLOCKS))
 blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                  const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                  const float4* __restrict__ rgb_thr, const float* __restrict__ obj_feats,
@@ -37,12 +43,13 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   const uint32_t wx0 = blockIdx.x * TILE_X + (warp & 1) * WARP_W, wy0 = blockIdx.y * TILE_Y + (warp >> 1) * WARP_H;
   const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-  const float pxf = (float)px, pyf = (float)py, wx0f = (float)wx0, wy0f = (float)wy0;
+  const float npxf = -(float)px, npyf = -(float)py, wx0f = (float)wx0, wy0f = (float)wy0;
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   int todo = (int)(range.y - range.x);
 
   bool done = !inside;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
+  // object channels as eight packed pairs: sm_100a's FFMA2 (fma.rn.f32x2) does two channels per issue slot
   float O[K > 0 ? K : 1];
 #pragma unroll
   for (int k = 0; k < (K > 0 ? K : 1); k++) O[k] = 0.f;
@@ -79,24 +86,23 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         { const uint32_t act = __ballot_sync(__activemask(), !done); GSR_STAT(5, __popc(act)); }
 #endif
         const float4 a = S.a[j];
-        const float4 b = S.b[j];
-        const float dx = fpx::sub(a.x, pxf), dy = fpx::sub(a.y, pyf);
-        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
+        const float power = gauss_power_packed(a, S.b[j].x, npyf, npxf);
         // Straight-line evaluation: every lane computes alpha, and the reference's three `continue`s
         // (forward.cu:336-349) become predicates on the accumulation -- same values, same decisions, no divergent
         // region in the loop (the per-Gaussian threshold pre-test is left to the rectangle cull).
         const float4 c = S.c[j];
         float wobj = 0.f;  // alpha * T of this pair when it contributes (object channels only)
         const bool p1 = !done && !(power > 0.0f);
-        const float alpha = fminf(0.99f, fpx::mul(c.x, expf(power)));
+        const float alpha = fminf(0.99f, fpx::mul(c.w, expf(power)));
         const bool p2 = p1 && !(alpha < 1.0f / 255.0f);
         const float test_T = fpx::mul(T, fpx::sub(1.0f, alpha));
         const bool stop = p2 && test_T < 0.0001f;
         done = done || stop;
         if (p2 && !stop) {
-          C0 = fpx::fma_(T, fpx::mul(alpha, c.y), C0);
-          C1 = fpx::fma_(T, fpx::mul(alpha, c.z), C1);
-          C2 = fpx::fma_(T, fpx::mul(alpha, c.w), C2);
+          float m0, m1;
+          fpx::mul2_bcast(m0, m1, c.x, c.y, alpha);  // (alpha r, alpha g), then (C0, C1) += T * (.,.): FMUL2 + FFMA2
+          fpx::fma2_bcast(C0, C1, m0, m1, T);
+          C2 = fpx::fma_(T, fpx::mul(alpha, c.z), C2);
           if (K > 0) wobj = T * alpha;
           T = test_T;
           last_contributor = first + j + 1;
@@ -104,13 +110,14 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           atomicAdd(&g_blend_stats[4], 1ull);
 #endif
         }
-        if (K > 0 && __any_sync(0xffffffffu, wobj != 0.f)) {
+        if (K > 0) {  // every lane, wobj = 0 where the pair does not contribute (skipping entries without any
+                      // contributing lane measured slower: 0.555 vs 0.524 ms on C2, most kept entries contribute)
           // O_k += f_k * alpha * T (Gaussian-Grouping's extra channels: same weights as the colour, no background)
 #pragma unroll
           for (int q = 0; q < K / 4; q++) {
             const float4 f = s_obj[q][j];
-            O[4 * q] = fmaf(wobj, f.x, O[4 * q]); O[4 * q + 1] = fmaf(wobj, f.y, O[4 * q + 1]);
-            O[4 * q + 2] = fmaf(wobj, f.z, O[4 * q + 2]); O[4 * q + 3] = fmaf(wobj, f.w, O[4 * q + 3]);
+            fpx::fma2_bcast(O[4 * q], O[4 * q + 1], f.x, f.y, wobj);
+            fpx::fma2_bcast(O[4 * q + 2], O[4 * q + 3], f.z, f.w, wobj);
           }
         }
       }

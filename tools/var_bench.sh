@@ -1,7 +1,7 @@
 #!/bin/bash
-# times bench.py for each library variant in lib/var_*.so (kernel experiments)
+# times bench.py for each library variant in lib/var_*.so (kernel experiments); extra arguments go to bench.py
 for so in 3d-gaussian-splat-attack_b200/lib/var_*.so; do
-  GSR_B200_LIB=$PWD/$so timeout 200 python bench.py --steps 10 --no-cpu-baseline --no-e2e > gpurun_out/var.log 2>&1
+  GSR_B200_LIB=$PWD/$so timeout 200 python bench.py --steps 10 --no-cpu-baseline --no-e2e --no-drop-in "$@" > gpurun_out/var.log 2>&1
   python - "$so" <<PY
 import json,sys
 try:
