@@ -117,10 +117,15 @@ int gsr_debug_counters(uint64_t* out_host, int reset) {
   return blend_bwd_stats(out_host + 8, reset);
 }
 
+int gsr_debug_sort_profile(uint64_t* out_host, int reset) {
+  if (!out_host) { set_error("debug_sort_profile: NULL"); return GSR_ERR_INVALID; }
+  return sort_profile_read(out_host, reset);
+}
+
 size_t gsr_geom_bytes(int32_t P) { return Geom(nullptr, P).bytes; }
 size_t gsr_image_bytes(int32_t W, int32_t H) { return Image(nullptr, W, H).bytes; }
 size_t gsr_scratch_bytes(int32_t P, int64_t L_cap, int32_t, int32_t) { return Scratch(nullptr, P, L_cap).bytes; }
-size_t gsr_sort_temp_bytes(int64_t n) { return SortTemp(nullptr, n).bytes + align_up((size_t)n * 8) + align_up((size_t)n * 4); }
+size_t gsr_sort_temp_bytes(int64_t n) { return sort_temp_bytes(n, 64, 8) + align_up((size_t)n * 8) + align_up((size_t)n * 4); }
 
 int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void* scratch, size_t scratch_bytes,
                          uint32_t* num_rendered_dev, uint32_t* num_rendered_host, void* stream) {
@@ -139,7 +144,8 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   GSR_TRY(debug_sync(in, st, "preprocess"));
   // order the Gaussians by (depth bits, index): 4 passes, the result lands back in (dkeys_a, geom.perm)
   { StageScope ps(ST_SORT, st);
-    GSR_TRY(launch_sort_pairs_pingpong_u32(s.dkeys_a, g.perm, s.dkeys_b, s.dvals_b, in->P, 32, s.sort_temp, nullptr, false, st)); }
+    GSR_TRY(launch_sort_pairs_pingpong_u32(s.dkeys_a, g.perm, s.dkeys_b, s.dvals_b, in->P, nullptr,
+                                           make_sort_plan(in->P, 32, 4), s.sort_temp, false, st)); }
   GSR_TRY(debug_sync(in, st, "depth_sort"));
   { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, num_rendered_dev, st)); }
   GSR_TRY(debug_sync(in, st, "sorted_scan"));
@@ -156,8 +162,12 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   return GSR_OK;
 }
 
+// L = capacity of point_list / the tile-sort buffers in pairs.  n_dev == nullptr: L is also the exact pair count
+// (the host read it back).  n_dev != nullptr: the count is read on the device (speculative launch, the host has not
+// seen it yet); if it exceeds L the result is incomplete -- never out of bounds -- and the caller redoes the call.
 static int forward_binning_impl(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
-                                uint32_t* point_list, void* image, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+                                const uint32_t* n_dev, uint32_t* point_list, void* image, void* scratch,
+                                size_t scratch_bytes, cudaStream_t st) {
   if (!image || L < 0) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
   if (in->P == 0) return GSR_OK;
   if (!geom || !radii || !scratch || (L > 0 && !point_list)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
@@ -170,25 +180,26 @@ static int forward_binning_impl(const gsr_inputs* in, const void* geom, const in
   Scratch s(scratch, in->P, L);
   const int gx = (in->W + TILE_X - 1) / TILE_X, gy = (in->H + TILE_Y - 1) / TILE_Y;
   const int end_bit = (int)higher_msb((uint32_t)(gx * gy));
-  const int passes = (end_bit + 7) / 8;
+  const SortPlan plan = make_sort_plan(L, end_bit, 4);
+  const int passes = plan.passes;
   // pass p reads pair (p&1) and writes the other: start in the pair that makes the result land in point_list
   uint32_t* k0 = (passes & 1) ? s.tkeys_b : s.tkeys_a;
   uint32_t* k1 = (passes & 1) ? s.tkeys_a : s.tkeys_b;
   uint32_t* v0 = (passes & 1) ? s.vals_a : point_list;
   uint32_t* v1 = (passes & 1) ? point_list : s.vals_a;
   if (L > 0) {
-    // the tile-id sort has <= 2 passes for up to 65536 tiles: duplicate_tiles builds its digit histograms
-    const bool fused_hist = end_bit <= 16;
+    // up to two digits (65536 tiles): duplicate_tiles builds the sort's digit histograms
+    const bool fused_hist = passes <= 2;
     uint32_t* hist = nullptr;
     { StageScope ps(ST_DUPLICATE, st);
-      if (fused_hist) GSR_TRY(sort_prepare(s.sort_temp, L, passes, &hist, st));
-      GSR_TRY(launch_duplicate_tiles(in->P, g, gx, k0, v0, hist, end_bit, st)); }
+      if (fused_hist) GSR_TRY(sort_prepare(s.sort_temp, L, plan, &hist, st));
+      GSR_TRY(launch_duplicate_tiles(in->P, g, gx, k0, v0, hist, plan, L, st)); }
     GSR_TRY(debug_sync(in, st, "duplicate_tiles"));
     { StageScope ps(ST_SORT, st);
-      GSR_TRY(launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, L, end_bit, s.sort_temp, nullptr, fused_hist, st)); }
+      GSR_TRY(launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, L, n_dev, plan, s.sort_temp, fused_hist, st)); }
     GSR_TRY(debug_sync(in, st, "sort"));
   }
-  { StageScope ps(ST_RANGES, st); GSR_TRY(launch_tile_ranges(L, s.tkeys_a, im.ranges, gx * gy, st)); }
+  { StageScope ps(ST_RANGES, st); GSR_TRY(launch_tile_ranges(L, n_dev, s.tkeys_a, im.ranges, gx * gy, st)); }
   return debug_sync(in, st, "tile_ranges");
 }
 
@@ -211,7 +222,7 @@ static int forward_blend_impl(const gsr_inputs* in, const void* geom, const uint
 int gsr_forward_binning(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L, uint32_t* point_list,
                         void* image, void* scratch, size_t scratch_bytes, void* stream) {
   GSR_TRY(check_inputs(in));
-  return forward_binning_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, (cudaStream_t)stream);
+  return forward_binning_impl(in, geom, radii, L, nullptr, point_list, image, scratch, scratch_bytes, (cudaStream_t)stream);
 }
 
 int gsr_forward_blend(const gsr_inputs* in, const void* geom, const uint32_t* point_list, void* image,
@@ -225,7 +236,18 @@ int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* ra
                        void* stream) {
   GSR_TRY(check_inputs(in));
   if (!out_color || (in->K > 0 && !out_objects)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
-  GSR_TRY(forward_binning_impl(in, geom, radii, L, point_list, image, scratch, scratch_bytes, (cudaStream_t)stream));
+  GSR_TRY(forward_binning_impl(in, geom, radii, L, nullptr, point_list, image, scratch, scratch_bytes, (cudaStream_t)stream));
+  return forward_blend_impl(in, geom, point_list, image, out_color, out_objects, (cudaStream_t)stream);
+}
+
+int gsr_forward_render_speculative(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L_cap,
+                                   const uint32_t* num_rendered_dev, uint32_t* point_list, void* image, void* scratch,
+                                   size_t scratch_bytes, float* out_color, float* out_objects, void* stream) {
+  GSR_TRY(check_inputs(in));
+  if (!out_color || (in->K > 0 && !out_objects) || !num_rendered_dev) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  if (L_cap < 1) { set_error("forward_render_speculative: capacity must be >= 1"); return GSR_ERR_INVALID; }
+  GSR_TRY(forward_binning_impl(in, geom, radii, L_cap, num_rendered_dev, point_list, image, scratch, scratch_bytes,
+                               (cudaStream_t)stream));
   return forward_blend_impl(in, geom, point_list, image, out_color, out_objects, (cudaStream_t)stream);
 }
 
@@ -333,17 +355,42 @@ int gsr_sort_pairs_u64(const uint64_t* keys_in, uint64_t* keys_out, const uint32
   if (n == 0) return GSR_OK;
   if (temp_bytes < gsr_sort_temp_bytes(n)) { set_error("sort temp too small"); return GSR_ERR_CAPACITY; }
   Carver c(temp);
-  void* st_temp = c.take<char>(SortTemp(nullptr, n).bytes);
+  const SortPlan plan = make_sort_plan(n, end_bit, 8);
+  void* st_temp = c.take<char>(sort_temp_bytes(n, 64, 8));
   uint64_t* ktmp = c.take<uint64_t>((size_t)n);
   uint32_t* vtmp = c.take<uint32_t>((size_t)n);
-  const int passes = (end_bit + 7) / 8;
+  const int passes = plan.passes;
   uint64_t* k0 = (passes & 1) ? ktmp : keys_out;
   uint32_t* v0 = (passes & 1) ? vtmp : vals_out;
   uint64_t* k1 = (passes & 1) ? keys_out : ktmp;
   uint32_t* v1 = (passes & 1) ? vals_out : vtmp;
   GSR_CUDA_CHECK(cudaMemcpyAsync(k0, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
   GSR_CUDA_CHECK(cudaMemcpyAsync(v0, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
-  return launch_sort_pairs_pingpong(k0, v0, k1, v1, n, end_bit, st_temp, nullptr, st);
+  return launch_sort_pairs_pingpong(k0, v0, k1, v1, n, plan, st_temp, st);
+}
+
+size_t gsr_sort_u32_temp_bytes(int64_t n_cap) { return sort_temp_bytes(n_cap, 32, 4) + 2 * align_up((size_t)n_cap * 4); }
+
+int gsr_sort_pairs_u32(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                       int64_t n_cap, const uint32_t* n_dev, int32_t end_bit, void* temp, size_t temp_bytes,
+                       void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_cap < 0 || end_bit < 1 || end_bit > 32) { set_error("sort: bad n/end_bit"); return GSR_ERR_INVALID; }
+  if (n_cap == 0) return GSR_OK;
+  if (temp_bytes < gsr_sort_u32_temp_bytes(n_cap)) { set_error("sort temp too small"); return GSR_ERR_CAPACITY; }
+  const SortPlan plan = make_sort_plan(n_cap, end_bit, 4);
+  Carver c(temp);
+  void* st_temp = c.take<char>(sort_temp_bytes(n_cap, 32, 4));
+  uint32_t* ktmp = c.take<uint32_t>((size_t)n_cap);
+  uint32_t* vtmp = c.take<uint32_t>((size_t)n_cap);
+  const int passes = plan.passes;
+  uint32_t* k0 = (passes & 1) ? ktmp : keys_out;
+  uint32_t* v0 = (passes & 1) ? vtmp : vals_out;
+  uint32_t* k1 = (passes & 1) ? keys_out : ktmp;
+  uint32_t* v1 = (passes & 1) ? vals_out : vtmp;
+  if (keys_in != k0) GSR_CUDA_CHECK(cudaMemcpyAsync(k0, keys_in, (size_t)n_cap * 4, cudaMemcpyDeviceToDevice, st));
+  if (vals_in != v0) GSR_CUDA_CHECK(cudaMemcpyAsync(v0, vals_in, (size_t)n_cap * 4, cudaMemcpyDeviceToDevice, st));
+  return launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, n_cap, n_dev, plan, st_temp, false, st);
 }
 
 int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64_t L, const void* geom,

@@ -110,8 +110,10 @@ __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets_sorted,
                        const uint32_t* __restrict__ tiles_touched, const ushort4* __restrict__ rects, int gx,
                        uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ hist,
-                       uint32_t mask1) {
-  // mask1 <= 255 whenever hist != nullptr (end_bit <= 16, launch_duplicate_tiles): sh[] has two 256-bin rows
+                       uint32_t mask0, int shift1, uint32_t mask1, uint32_t cap) {
+  // hist != nullptr: the tile sort has at most two digits, (key & mask0) and ((key >> shift1) & mask1), both
+  // <= 8 bits wide (launch_duplicate_tiles): sh[] has two 256-bin rows.  Pairs beyond `cap` (the capacity of a
+  // speculative launch that was sized before the count was known) are neither written nor counted.
   __shared__ uint32_t sh[2 * 256];
   for (int k = threadIdx.x; k < 2 * 256; k += DUP_THREADS) sh[k] = 0;
   __syncthreads();
@@ -133,11 +135,13 @@ duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t*
       uint32_t x = 0, y = 0;
       for (uint32_t t = 0; t < area; t++) {
         const uint32_t key = (y0 + y) * gx + x0 + x;
-        keys[off + t] = key;
-        vals[off + t] = id;
-        if (hist) {
-          atomicAdd(&sh[key & 255u], 1u);
-          atomicAdd(&sh[256 + ((key >> 8) & mask1)], 1u);
+        if (off + t < cap) {
+          keys[off + t] = key;
+          vals[off + t] = id;
+          if (hist) {
+            atomicAdd(&sh[key & mask0], 1u);
+            atomicAdd(&sh[256 + ((key >> shift1) & mask1)], 1u);
+          }
         }
         if (++x == w) { x = 0; y++; }
       }
@@ -152,11 +156,13 @@ duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t*
       for (uint32_t t = lane; t < a; t += 32) {
         const uint32_t y = t / bw, x = t - y * bw;
         const uint32_t key = (by + y) * gx + bx + x;
-        keys[o + t] = key;
-        vals[o + t] = bid;
-        if (hist) {
-          atomicAdd(&sh[key & 255u], 1u);
-          atomicAdd(&sh[256 + ((key >> 8) & mask1)], 1u);
+        if (o + t < cap) {
+          keys[o + t] = key;
+          vals[o + t] = bid;
+          if (hist) {
+            atomicAdd(&sh[key & mask0], 1u);
+            atomicAdd(&sh[256 + ((key >> shift1) & mask1)], 1u);
+          }
         }
       }
     }
@@ -168,21 +174,37 @@ duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t*
   }
 }
 
-// ranges[tile] = [first, one-past-last) index of that tile's run in the sorted tile-id list.
-__global__ void tile_ranges_kernel(int64_t L, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= L) return;
-  const uint32_t cur = keys[i];
-  if (i == 0) {
-    ranges[cur].x = 0;
+// ranges[tile] = [first, one-past-last) index of that tile's run in the sorted tile-id list; four list entries per
+// thread (one 16-byte load).  The list length may live on the device (n_dev, bounded by n_cap).
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(int64_t n_cap, const uint32_t* __restrict__ n_dev, const uint32_t* __restrict__ keys,
+                   uint2* __restrict__ ranges) {
+  int64_t n = n_cap;
+  if (n_dev) { const int64_t v = (int64_t)__ldg(n_dev); n = v < n_cap ? v : n_cap; }
+  const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i0 >= n) return;
+  uint32_t k[5];
+  k[0] = i0 ? keys[i0 - 1] : 0u;
+  if (i0 + 3 < n) {
+    const uint4 v = *reinterpret_cast<const uint4*>(keys + i0);
+    k[1] = v.x; k[2] = v.y; k[3] = v.z; k[4] = v.w;
   } else {
-    const uint32_t prev = keys[i - 1];
-    if (cur != prev) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) k[j + 1] = i0 + j < n ? keys[i0 + j] : 0u;
+  }
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const int64_t i = i0 + j;
+    if (i >= n) break;
+    const uint32_t cur = k[j + 1], prev = k[j];
+    if (i == 0) {
+      ranges[cur].x = 0;
+    } else if (cur != prev) {
       ranges[prev].y = (uint32_t)i;
       ranges[cur].x = (uint32_t)i;
     }
+    if (i == n - 1) ranges[cur].y = (uint32_t)n;
   }
-  if (i == L - 1) ranges[cur].y = (uint32_t)L;
 }
 
 // debug only: the reference's sorted 64-bit keys, rebuilt from the sorted tile ids and the point list
@@ -213,14 +235,19 @@ int launch_index_scan(int P, const Geom& g, Scratch& s, uint32_t* out, cudaStrea
   return GSR_OK;
 }
 
-// end_bit <= 16: the tile-id sort has at most two 8-bit passes, whose histograms are built here
+// hist != nullptr (only when the tile sort's plan has at most two digits): the sort's digit histograms are built
+// here.  cap = capacity of tile_keys / vals in pairs.
 int launch_duplicate_tiles(int P, const Geom& g, int gx, uint32_t* tile_keys, uint32_t* vals, uint32_t* hist,
-                           int end_bit, cudaStream_t st) {
+                           const SortPlan& plan, int64_t cap, cudaStream_t st) {
   const int nchunks = (P + DUP_THREADS - 1) / DUP_THREADS;
   const int blocks = nchunks < 148 * 6 ? nchunks : 148 * 6;
-  const uint32_t mask1 = end_bit > 8 ? (1u << (end_bit - 8)) - 1u : 0u;
+  if (hist && plan.passes > 2) { set_error("duplicate_tiles: fused histograms need <= 2 digits"); return GSR_ERR_INVALID; }
+  const uint32_t mask0 = (1u << plan.bits[0]) - 1u;
+  const int shift1 = plan.passes > 1 ? plan.shift[1] : 0;
+  const uint32_t mask1 = plan.passes > 1 ? (1u << plan.bits[1]) - 1u : 0u;
+  const uint32_t cap32 = cap > 0xffffffffll ? 0xffffffffu : (uint32_t)cap;
   duplicate_tiles_kernel<<<blocks, DUP_THREADS, 0, st>>>(P, g.perm, g.offsets_sorted, g.tiles_touched, g.rects, gx,
-                                                         tile_keys, vals, hist, mask1);
+                                                         tile_keys, vals, hist, mask0, shift1, mask1, cap32);
   GSR_LAUNCH_CHECK("duplicate_tiles_kernel");
   return GSR_OK;
 }
@@ -234,10 +261,11 @@ int launch_rebuild_keys(int64_t L, const uint32_t* tile_keys, const uint32_t* po
   return GSR_OK;
 }
 
-int launch_tile_ranges(int64_t L, const uint32_t* keys_sorted, uint2* ranges, int tiles, cudaStream_t st) {
+int launch_tile_ranges(int64_t L_cap, const uint32_t* n_dev, const uint32_t* keys_sorted, uint2* ranges, int tiles,
+                       cudaStream_t st) {
   GSR_CUDA_CHECK(cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), st));
-  if (L > 0) {
-    tile_ranges_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(L, keys_sorted, ranges);
+  if (L_cap > 0) {
+    tile_ranges_kernel<<<(unsigned)((L_cap + 1023) / 1024), 256, 0, st>>>(L_cap, n_dev, keys_sorted, ranges);
     GSR_LAUNCH_CHECK("tile_ranges_kernel");
   }
   return GSR_OK;

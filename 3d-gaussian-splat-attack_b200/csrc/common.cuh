@@ -102,31 +102,49 @@ constexpr int SORT_THREADS = 256;
 #ifndef GSR_SORT_ITEMS
 #define GSR_SORT_ITEMS 16
 #endif
-constexpr int SORT_ITEMS = GSR_SORT_ITEMS;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 pairs per block
+#ifndef GSR_SORT_ITEMS_SMALL
+#define GSR_SORT_ITEMS_SMALL 8
+#endif
+constexpr int SORT_ITEMS = GSR_SORT_ITEMS;              // 4096 pairs per block
+constexpr int SORT_ITEMS_SMALL = GSR_SORT_ITEMS_SMALL;  // 2048 pairs per block for sorts of <= SORT_SMALL_TILE_LIMIT pairs
+constexpr int64_t SORT_SMALL_TILE_LIMIT = (int64_t)1 << 22;
+constexpr int64_t SORT_SMALL_LIMIT = (int64_t)1 << 30;  // below: 32-bit look-back words, above: 64-bit
 constexpr int SORT_MAX_PASSES = 8;
-inline int64_t sort_tiles(int64_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }
+constexpr int SORT_LB_GROUP = 16;  // tiles per look-back group (radix_sort.cu)
+inline int64_t sort_tiles(int64_t n, int items) { return (n + SORT_THREADS * items - 1) / (SORT_THREADS * items); }
+
+// Digit layout and tile size of one LSD sort (radix_sort.cu: make_sort_plan).
+struct SortPlan {
+  int end_bit = 0, passes = 0, items = SORT_ITEMS;
+  int shift[SORT_MAX_PASSES] = {0}, bits[SORT_MAX_PASSES] = {0};
+};
+SortPlan make_sort_plan(int64_t n_cap, int end_bit, int key_bytes);
 
 struct SortTemp {
-  uint32_t* hist;     // [SORT_MAX_PASSES][256] digit histograms -> exclusive offsets
+  uint32_t* hist;     // [SORT_MAX_PASSES][256] digit histograms (raw counts; every scatter block scans them)
   uint32_t* tickets;  // [SORT_MAX_PASSES] dynamic tile ids
-  uint32_t* status;   // [SORT_MAX_PASSES][tiles][256] decoupled look-back words
-  size_t status_off, pass_stride;
+  uint32_t* status;   // [passes]{[tiles][256] tile words, [groups][256] group words}: decoupled look-back
+  size_t status_off, pass_stride, group_off;
   size_t bytes;
-  SortTemp(void* buf, int64_t n) {
+  SortTemp(void* buf, int64_t n_cap, int passes, int items) {
     Carver c(buf);
     hist = c.take<uint32_t>(SORT_MAX_PASSES * 256);
     tickets = c.take<uint32_t>(64);
     status_off = c.off;
-    // 32-bit look-back words below 2^30 pairs, 64-bit words above (radix_sort.cu)
-    const size_t word = n >= ((int64_t)1 << 30) ? 8 : 4;
-    pass_stride = (size_t)sort_tiles(n) * 256 * word;
-    status = (uint32_t*)c.take<char>((size_t)SORT_MAX_PASSES * pass_stride);
+    const size_t word = n_cap >= SORT_SMALL_LIMIT ? 8 : 4;
+    const size_t tiles = (size_t)sort_tiles(n_cap, items);
+    group_off = tiles * 256 * word;
+    pass_stride = group_off + (tiles + SORT_LB_GROUP - 1) / SORT_LB_GROUP * 256 * word;
+    status = (uint32_t*)c.take<char>((size_t)passes * pass_stride);
     bytes = c.off;
   }
   // prefix of the buffer that must be zeroed before a sort of `passes` passes
   size_t zero_bytes(int passes) const { return status_off + (size_t)passes * pass_stride; }
 };
+inline size_t sort_temp_bytes(int64_t n_cap, int end_bit, int key_bytes) {
+  const SortPlan p = make_sort_plan(n_cap, end_bit, key_bytes);
+  return SortTemp(nullptr, n_cap, p.passes, p.items).bytes;
+}
 
 // Reusable scratch (not needed after the call that used it returns).
 //
@@ -167,7 +185,9 @@ struct Scratch {
     tkeys_a = c.take<uint32_t>((size_t)L);
     tkeys_b = c.take<uint32_t>((size_t)L);
     vals_a = c.take<uint32_t>((size_t)L);
-    sort_temp = c.take<char>(SortTemp(nullptr, L > P ? L : (int64_t)P).bytes);
+    // shared by the depth sort (P pairs, 32 key bits) and the tile sort (L pairs, <= 32 key bits)
+    const size_t ta = sort_temp_bytes((int64_t)P, 32, 4), tb = sort_temp_bytes(L, 32, 4);
+    sort_temp = c.take<char>(ta > tb ? ta : tb);
     bytes = c.off;
   }
 };
@@ -218,15 +238,17 @@ int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch
 int launch_sorted_scan(int P, const Geom& g, Scratch& s, uint32_t* num_rendered_dev, cudaStream_t st);
 int launch_index_scan(int P, const Geom& g, Scratch& s, uint32_t* out, cudaStream_t st);
 int launch_duplicate_tiles(int P, const Geom& g, int gx, uint32_t* tile_keys, uint32_t* vals, uint32_t* hist,
-                           int end_bit, cudaStream_t st);
-int sort_prepare(void* temp, int64_t n, int passes, uint32_t** hist_out, cudaStream_t st);
+                           const SortPlan& plan, int64_t cap, cudaStream_t st);
+int sort_prepare(void* temp, int64_t n_cap, const SortPlan& plan, uint32_t** hist_out, cudaStream_t st);
 int launch_rebuild_keys(int64_t L, const uint32_t* tile_keys, const uint32_t* point_list, const float* depths,
                         uint64_t* keys_out, cudaStream_t st);
 int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
-                               int end_bit, void* temp, int* passes_out, cudaStream_t st);
-int launch_sort_pairs_pingpong_u32(uint32_t* keys0, uint32_t* vals0, uint32_t* keys1, uint32_t* vals1, int64_t n,
-                                   int end_bit, void* temp, int* passes_out, bool hist_ready, cudaStream_t st);
-int launch_tile_ranges(int64_t L, const uint32_t* tile_keys_sorted, uint2* ranges, int tiles, cudaStream_t st);
+                               const SortPlan& plan, void* temp, cudaStream_t st);
+int launch_sort_pairs_pingpong_u32(uint32_t* keys0, uint32_t* vals0, uint32_t* keys1, uint32_t* vals1, int64_t n_cap,
+                                   const uint32_t* n_dev, const SortPlan& plan, void* temp, bool hist_ready,
+                                   cudaStream_t st);
+int launch_tile_ranges(int64_t L_cap, const uint32_t* n_dev, const uint32_t* tile_keys_sorted, uint2* ranges, int tiles,
+                       cudaStream_t st);
 int launch_blend_fwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
                      float* out_color, float* out_objects, cudaStream_t st);
 int launch_blend_bwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,
@@ -243,6 +265,7 @@ int launch_detector_scale(const float* x, float* y, const float* dy, float* dx, 
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 
 uint32_t higher_msb(uint32_t n);
+int sort_profile_read(uint64_t* out_host, int reset);
 int blend_fwd_stats(uint64_t* out_host, int reset);
 int blend_bwd_stats(uint64_t* out_host, int reset);
 

@@ -16,6 +16,7 @@ There is no CPU path: non-CUDA tensors raise.
 """
 from typing import NamedTuple
 import ctypes as C
+import os
 
 import torch
 import torch.nn as nn
@@ -41,6 +42,8 @@ class _DeviceState:
         self.scratch = torch.empty(0, dtype=torch.uint8, device=device)
         self.count_dev = torch.zeros(1, dtype=torch.int32, device=device)
         self.count_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self.ev_count = torch.cuda.Event()
+        self.last_L = {}  # (P, W, H) -> duplicate count of the previous view of that shape (sizes the next launch)
 
     def ensure_scratch(self, nbytes):
         if self.scratch.numel() < nbytes:
@@ -50,6 +53,7 @@ class _DeviceState:
 
 
 _states = {}
+SPECULATE = os.environ.get("GSR_SPECULATE", "1") != "0"  # gsr_forward_render_speculative in steady state
 
 
 def _state(device):
@@ -127,16 +131,34 @@ def _run_forward(rs, P, M, K, want_obj, means3D_c, sh_c, col_c, op_c, sc_c, rot_
             geom = torch.empty(lib.gsr_geom_bytes(P), dtype=torch.uint8, device=dev)
             image = torch.empty(lib.gsr_image_bytes(W, H), dtype=torch.uint8, device=dev)
             scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, 0, W, H))
+            # Steady state without a GPU bubble at the read-back of the duplicate count (rasterizer_impl.cu:281):
+            # when a previous view of this shape is known, point_list / scratch are sized for 1.25 x its count and
+            # phase 2 is queued at once, reading the actual count on the device; the host then waits only for
+            # phase 1 (while phase 2 executes) and repeats phase 2 with the exact size in the rare overflow.
+            key = (P, W, H)
+            guess = st.last_L.get(key, 0) if SPECULATE and not rs.debug and not rs.prefiltered else 0
+            L_cap = max(int(guess * 1.25) + 4096, 1) if guess else 0
+            scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, L_cap, W, H))
             _abi.check(lib.gsr_forward_geometry(C.byref(inp), _ptr(geom), _ptr(radii), _ptr(scratch),
                                                 scratch.numel(), _ptr(st.count_dev),
                                                 C.c_void_p(st.count_host.data_ptr()), sp), "forward_geometry")
-            stream.synchronize()  # the one host sync per view (reference: rasterizer_impl.cu:281)
+            if L_cap:
+                st.ev_count.record(stream)
+                point_list = torch.empty((L_cap,), dtype=torch.int32, device=dev)
+                _abi.check(lib.gsr_forward_render_speculative(
+                    C.byref(inp), _ptr(geom), _ptr(radii), L_cap, _ptr(st.count_dev), _ptr(point_list), _ptr(image),
+                    _ptr(scratch), scratch.numel(), _ptr(color), _ptr(objects), sp), "forward_render_speculative")
+                st.ev_count.synchronize()  # phase 1 only; phase 2 is running
+            else:
+                stream.synchronize()  # first view of this shape: the one host sync (reference: rasterizer_impl.cu:281)
             L = int(st.count_host.item()) & 0xFFFFFFFF
-            point_list = torch.empty((max(L, 1),), dtype=torch.int32, device=dev)
-            scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, L, W, H))
-            _abi.check(lib.gsr_forward_render(C.byref(inp), _ptr(geom), _ptr(radii), L, _ptr(point_list),
-                                              _ptr(image), _ptr(scratch), scratch.numel(), _ptr(color),
-                                              _ptr(objects), sp), "forward_render")
+            st.last_L[key] = L
+            if L > L_cap:  # not speculated, or the guess was too small: phase 2 with the exact size
+                point_list = torch.empty((max(L, 1),), dtype=torch.int32, device=dev)
+                scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, L, W, H))
+                _abi.check(lib.gsr_forward_render(C.byref(inp), _ptr(geom), _ptr(radii), L, _ptr(point_list),
+                                                  _ptr(image), _ptr(scratch), scratch.numel(), _ptr(color),
+                                                  _ptr(objects), sp), "forward_render")
             if rs.debug:
                 stream.synchronize()
     return color, objects, radii, L, geom, point_list, image

@@ -13,7 +13,7 @@ LIB_PATH = os.environ.get("GSR_B200_LIB") or os.path.join(_ROOT, "lib", "libgsr_
 CSRC_DIR = os.path.join(_ROOT, "csrc")
 
 GSR_OK, GSR_ERR_INVALID, GSR_ERR_CUDA, GSR_ERR_CAPACITY, GSR_ERR_PREFILTERED = 0, -1, -2, -3, -4
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class GsrInputs(C.Structure):
@@ -42,6 +42,9 @@ EXPORTS = {
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_forward_render": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsr_forward_render_speculative": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
+                                                 C.c_void_p]),
     "gsr_forward_binning": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_size_t, C.c_void_p]),
     "gsr_forward_blend": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -61,10 +64,14 @@ EXPORTS = {
     "gsr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_sort_pairs_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),
+    "gsr_sort_u32_temp_bytes": (C.c_size_t, [C.c_int64]),
+    "gsr_sort_pairs_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32,
+                                     C.c_void_p, C.c_size_t, C.c_void_p]),
     "gsr_profile_enable": (C.c_int, [C.c_int]),
     "gsr_profile_read": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gsr_launch_count": (C.c_int64, [C.c_int]),
     "gsr_debug_counters": (C.c_int, [C.c_void_p, C.c_int]),
+    "gsr_debug_sort_profile": (C.c_int, [C.c_void_p, C.c_int]),
     "gsr_debug_fetch": (C.c_int64, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
 }

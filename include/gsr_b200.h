@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 2
+#define GSR_ABI_VERSION 3
 
 typedef enum {
   GSR_OK = 0,
@@ -101,6 +101,18 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
 int gsr_forward_render(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L,
                        uint32_t* point_list, void* image, void* scratch, size_t scratch_bytes,
                        float* out_color, float* out_objects, void* stream);
+
+/* ---- forward, phase 2 WITHOUT the host knowing L (replaces the blocking read-back of rasterizer_impl.cu:281 in
+ *      steady state): point_list and scratch are sized for L_cap pairs (e.g. 1.25 x the previous view's L) and the
+ *      kernels read the actual count from num_rendered_dev (the word phase 1 wrote).  Grids are sized from L_cap,
+ *      surplus blocks leave at once.  If the count turns out larger than L_cap nothing is written out of bounds,
+ *      but the tile lists are incomplete: the caller -- which reads num_rendered_host once phase 1's kernels have
+ *      run, while phase 2 is already executing -- must then repeat phase 2 through gsr_forward_render with the
+ *      exact L and buffers of that size. ---- */
+int gsr_forward_render_speculative(const gsr_inputs* in, const void* geom, const int32_t* radii, int64_t L_cap,
+                                   const uint32_t* num_rendered_dev, uint32_t* point_list, void* image,
+                                   void* scratch, size_t scratch_bytes, float* out_color, float* out_objects,
+                                   void* stream);
 
 /* ---- phase 2 in two calls, so that a driver can put them on different streams: binning (duplicateWithKeys + sort +
  *      identifyTileRanges; uses `scratch`, writes point_list and the tile ranges inside `image`) and blending
@@ -173,6 +185,14 @@ int gsr_detector_scale(const float* x, float* y, const float* dL_dy, float* dL_d
 size_t gsr_sort_temp_bytes(int64_t n);
 int gsr_sort_pairs_u64(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
                        int64_t n, int32_t end_bit, void* temp, size_t temp_bytes, void* stream);
+/* The same sort on (u32 key, u32 value) pairs -- the form the forward pass uses (depth bits of P Gaussians, then tile
+ * ids of L pairs).  The pair count may live on the device: n_dev (device u32, or NULL) holds it, n_cap bounds it and
+ * sizes every buffer (keys_in / vals_in / keys_out / vals_out hold n_cap elements; the first min(*n_dev, n_cap) are
+ * sorted).  keys_in == keys_out (and vals) is allowed when the pass count is even.  temp >= gsr_sort_u32_temp_bytes. */
+size_t gsr_sort_u32_temp_bytes(int64_t n_cap);
+int gsr_sort_pairs_u32(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                       int64_t n_cap, const uint32_t* n_dev, int32_t end_bit, void* temp, size_t temp_bytes,
+                       void* stream);
 
 /* Copies internal arrays of a finished forward out for inspection. name is one of: "depths",
  * "means2D", "cov3D", "conic_opacity", "rgb", "clamped", "tiles_touched", "point_offsets", "rects",
@@ -197,6 +217,9 @@ int64_t gsr_launch_count(int reset);
 /* 16 counters of the blend kernels (8 forward, 8 backward), non-zero only in a `make STATS=1` build:
  * cull rounds, entries tested, entries kept, warp evaluations with a hit, contributing pairs, active lanes. */
 int gsr_debug_counters(uint64_t* out_host, int reset);
+/* Cycle counts per phase of the sort's scatter kernel (zeros unless built with -DGSR_SORT_PROFILE):
+ * out_host[8] = tiles, load, rank, count+scan, look-back, stage, write-out, -. */
+int gsr_debug_sort_profile(uint64_t* out_host, int reset);
 
 /* Host helper: number of key bits the tile id needs (getHigherMsb, rasterizer_impl.cu:35-50). */
 uint32_t gsr_higher_msb(uint32_t n);
