@@ -78,14 +78,6 @@ static int debug_sync(const gsr_inputs* in, cudaStream_t st, const char* stage) 
 }
 #define GSR_TRY(x) do { int _r = (x); if (_r != GSR_OK) return _r; } while (0)
 
-// Publishes the duplicate count to pinned (device-mapped) host memory with a store instead of a D2H memcpy:
-// a memcpy would queue on the device-to-host copy engine behind any large transfer another stream has in
-// flight (pipeline.HostStepPipeline drains 236 MB of gradients while the next step's forward needs this word).
-__global__ void publish_count_kernel(const uint32_t* __restrict__ dev, volatile uint32_t* host) {
-  *host = *dev;
-  __threadfence_system();
-}
-
 }  // namespace gsr
 
 using namespace gsr;
@@ -147,12 +139,8 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
     GSR_TRY(launch_sort_pairs_pingpong_u32(s.dkeys_a, g.perm, s.dkeys_b, s.dvals_b, in->P, nullptr,
                                            make_sort_plan(in->P, 32, 4), s.sort_temp, false, st)); }
   GSR_TRY(debug_sync(in, st, "depth_sort"));
-  { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, num_rendered_dev, st)); }
+  { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, num_rendered_dev, num_rendered_host, st)); }
   GSR_TRY(debug_sync(in, st, "sorted_scan"));
-  if (num_rendered_host) {
-    publish_count_kernel<<<1, 1, 0, st>>>(num_rendered_dev, num_rendered_host);
-    GSR_LAUNCH_CHECK("publish_count_kernel");
-  }
   if (in->prefiltered) {
     uint32_t flag = 0;
     GSR_CUDA_CHECK(cudaMemcpyAsync(&flag, s.flags, 4, cudaMemcpyDeviceToHost, st));

@@ -24,7 +24,7 @@ __device__ __forceinline__ unsigned long long pack_status(uint32_t flag, uint32_
 __global__ void __launch_bounds__(256)
 scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ tiles_touched,
                   uint32_t* __restrict__ offsets, unsigned long long* status, uint32_t* ticket,
-                  uint32_t* __restrict__ total_out, int nblocks) {
+                  uint32_t* __restrict__ total_out, volatile uint32_t* total_host, int nblocks) {
   __shared__ uint32_t s_tile, s_warp[8], s_prefix;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);  // blocks are numbered in start order -> look-back cannot deadlock
@@ -88,7 +88,13 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __re
     }
     if (lane == 0) {
       s_prefix = excl;
-      if (total_out && (int)tile == nblocks - 1) *total_out = excl + block_total;
+      if (total_out && (int)tile == nblocks - 1) {
+        *total_out = excl + block_total;
+        // the count also goes to pinned (device-mapped) host memory with a plain store instead of a D2H memcpy: a
+        // memcpy would queue on the copy engine behind any bulk transfer another stream has in flight
+        // (pipeline.HostStepPipeline drains 236 MB of gradients while the next step's forward needs this word)
+        if (total_host) { *total_host = excl + block_total; __threadfence_system(); }
+      }
     }
   }
   __syncthreads();
@@ -217,10 +223,11 @@ __global__ void rebuild_keys_kernel(int64_t L, const uint32_t* __restrict__ tile
 
 }  // namespace
 
-int launch_sorted_scan(int P, const Geom& g, Scratch& s, uint32_t* num_rendered_dev, cudaStream_t st) {
+int launch_sorted_scan(int P, const Geom& g, Scratch& s, uint32_t* num_rendered_dev, uint32_t* num_rendered_host,
+                       cudaStream_t st) {
   const int nb = (P + SCAN_ITEMS - 1) / SCAN_ITEMS;
   scan_tiles_kernel<<<nb, 256, 0, st>>>(P, g.perm, g.tiles_touched, g.offsets_sorted, s.scan2_status, s.scan_ticket + 1,
-                                        num_rendered_dev, nb);
+                                        num_rendered_dev, num_rendered_host, nb);
   GSR_LAUNCH_CHECK("scan_tiles_kernel");
   return GSR_OK;
 }
@@ -230,7 +237,7 @@ int launch_index_scan(int P, const Geom& g, Scratch& s, uint32_t* out, cudaStrea
   const int nb = (P + SCAN_ITEMS - 1) / SCAN_ITEMS;
   GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_status, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
   GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_ticket, 0, sizeof(uint32_t), st));
-  scan_tiles_kernel<<<nb, 256, 0, st>>>(P, nullptr, g.tiles_touched, out, s.scan_status, s.scan_ticket, nullptr, nb);
+  scan_tiles_kernel<<<nb, 256, 0, st>>>(P, nullptr, g.tiles_touched, out, s.scan_status, s.scan_ticket, nullptr, nullptr, nb);
   GSR_LAUNCH_CHECK("scan_tiles_kernel");
   return GSR_OK;
 }

@@ -62,10 +62,14 @@ sort_histogram_kernel(const KeyT* __restrict__ keys, int64_t n_cap, const uint32
   __syncthreads();
   const int64_t n = device_count(n_cap, n_dev);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
-  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+  // whole warps iterate together (the match below names every lane): the bound is the warp's first index
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i - 4 * (threadIdx.x & 31) < n; i += stride) {
     KeyT k[4];
     int m = 4;
-    if (i + 3 < n) {  // the key array is 16-byte aligned (caller's buffer carving): one vector load
+    if (i >= n) {
+      m = 0;
+      for (int j = 0; j < 4; j++) k[j] = (KeyT)0;
+    } else if (i + 3 < n) {  // the key array is 16-byte aligned (caller's buffer carving): one vector load
       if (sizeof(KeyT) == 4) {
         const uint4 v = *reinterpret_cast<const uint4*>(keys + i);
         k[0] = (KeyT)v.x; k[1] = (KeyT)v.y; k[2] = (KeyT)v.z; k[3] = (KeyT)v.w;
@@ -80,9 +84,22 @@ sort_histogram_kernel(const KeyT* __restrict__ keys, int64_t n_cap, const uint32
     for (int p = 0; p < passes; p++) {
       const int sft = dl.shift[p];
       const uint32_t msk = dl.mask[p];
+      if (p == passes - 1 && passes > 1) {
+        // the most significant digit of real keys (exponent bits of a depth, high bits of a tile id) has a few
+        // populated bins: one atomic per group of equal digits in the warp instead of 32 on the same word (MATCH.ANY
+        // costs a trip per distinct value, so it is cheap exactly here)
+        const uint32_t lt = (1u << (threadIdx.x & 31)) - 1u;
 #pragma unroll
-      for (int j = 0; j < 4; j++)
-        if (j < m) atomicAdd(&sh[p * 256 + ((uint32_t)(k[j] >> sft) & msk)], 1u);
+        for (int j = 0; j < 4; j++) {
+          const uint32_t d = j < m ? (uint32_t)(k[j] >> sft) & msk : 0xffffffffu;
+          const uint32_t peers = __match_any_sync(0xffffffffu, d);
+          if (j < m && (peers & lt) == 0) atomicAdd(&sh[p * 256 + d], (uint32_t)__popc(peers));
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+          if (j < m) atomicAdd(&sh[p * 256 + ((uint32_t)(k[j] >> sft) & msk)], 1u);
+      }
     }
   }
   __syncthreads();

@@ -182,7 +182,9 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {scene['P']} Gaussians SH3, {c['image_width']}x{c['image_height']}, fwd+bwd",
                    "views_per_step": args.cpu_sample_views, "note": "reference has no CPU rasterizer; this is the CPU "
-                   "restatement of its CUDA math (oracle/cpu_ref.cpp) on all host cores"},
+                   "restatement of its CUDA math (oracle/cpu_ref.cpp) on all host cores.  A full C2 view takes ~2.3 s "
+                   "of CPU time, so this arm is bounded to min(--steps, 3) steps of --cpu-sample-views view(s) and at "
+                   "most 1 warm-up (steps / warmup in this line are the ones actually run)"},
         "cpu_baseline": {"value": vps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": vps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -411,7 +413,11 @@ def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
     end_bit = 32 + max(1, int(tiles).bit_length())
     passes = (end_bit + 7) // 8
     HW = wl.W * wl.H
-    alg = {  # algorithmic bytes per launch (per view)
+    # Bytes per launch (per view).  alg_ref = SURVEY.md 8(d): what the REFERENCE algorithm must move (64-bit keys, six
+    # 8-bit sort passes, ...).  alg_own = what THIS design must move: Gaussians ordered by a
+    # 32-bit depth sort of P pairs (histogram read + 4 passes), tile ids of L pairs in 2 passes with the histogram built
+    # by the emitting kernel, 4-byte tile ids in the range pass.  hbm_frac is computed on alg_own.
+    alg_ref = {
         "preprocess_fwd": 311 * V + 20 * (P - V),
         "duplicate_keys": 20 * P + 12 * L,
         "sort": (8 + 24 * passes) * L,
@@ -420,27 +426,54 @@ def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
         "blend_bwd": 40 * L + 20 * HW + 36 * L,
         "preprocess_bwd": 559 * V + 300 * P,
     }
-    # blend stages are FP32-issue bound: instructions per examined (pixel, Gaussian) pair
-    fp32_instr = {"blend_fwd": 20, "blend_bwd": 45}
-    fp32_peak = 148 * 128 * sm_max_mhz * 1e6  # lane-instructions / s
+    tile_passes = (max(1, int(tiles).bit_length()) + 7) // 8
+    alg_own = dict(alg_ref)
+    alg_own["duplicate_keys"] = (12 * P) + (12 * P + 8 * V + 8 * L)   # depth-order scan + emission of 8-byte pairs
+    alg_own["sort"] = (4 + 16 * 4) * P + 16 * tile_passes * L            # depth sort + tile sort
+    alg_own["tile_ranges"] = 4 * L + 8 * tiles
+    cap = {}
+    for nm in ("r2_traffic.json", "r1_traffic.json"):  # committed `ncu --set full` capture of one view (tools/ncu_traffic.py)
+        try:
+            cap = json.load(open(os.path.join(ROOT, "profiles", nm)))
+            cap["_file"] = "profiles/" + nm
+            break
+        except Exception:
+            continue
+    # blend stages are instruction-issue bound: 148 SMs x 4 schedulers x clock warp-instructions / s
+    ref_lane_instr = {"blend_fwd": 20, "blend_bwd": 45}  # lane-instructions per examined pair, reference algorithm
+    fp32_peak = 148 * 128 * sm_max_mhz * 1e6   # lane-instructions / s
+    issue_peak = 148 * 4 * sm_max_mhz * 1e6    # warp-instructions / s
     out, total = {}, 0.0
     views = max(int(calls[_abi.STAGES.index("blend_fwd")]), 1)
     for i, name in enumerate(_abi.STAGES):
         avg = float(ms[i]) / views  # a stage may be recorded more than once per view (two sorts)
         total += avg
-        e = {"ms": avg, "calls": int(calls[i]), "alg_bytes": int(alg[name]),
-             "hbm_gbs": alg[name] / (avg * 1e-3) / 1e9 if avg > 0 else None}
+        e = {"ms": avg, "calls": int(calls[i]), "alg_own_bytes": int(alg_own[name]), "alg_ref_bytes": int(alg_ref[name]),
+             "hbm_gbs": alg_own[name] / (avg * 1e-3) / 1e9 if avg > 0 else None}
         e["hbm_frac"] = e["hbm_gbs"] / hbm_peak if e["hbm_gbs"] else None
-        if name in fp32_instr:
-            e["bound"] = "fp32-issue"
+        e["hbm_frac_on_ref_bytes"] = alg_ref[name] / (avg * 1e-3) / 1e9 / hbm_peak if avg > 0 else None
+        c = cap.get({"sort": "sort_pass", "duplicate_keys": "duplicate_keys"}.get(name, name))
+        if c and name != "sort":  # (the sort stage is six launches; its per-launch capture is under stages.sort.ncu)
+            e["dram_bytes"] = c.get("dram_bytes_per_launch")
+            e["dram_bytes_source"] = cap.get("_file")
+        if name in ref_lane_instr:
+            e["bound"] = "issue"
             e["pairs_lower_bound"] = pairs
-            e["fp32_frac"] = pairs * fp32_instr[name] / (avg * 1e-3) / fp32_peak if avg > 0 else None
+            e["vs_reference_algorithm"] = pairs * ref_lane_instr[name] / (avg * 1e-3) / fp32_peak if avg > 0 else None
+            if c and c.get("warp_inst_executed_per_launch"):
+                e["warp_inst_per_launch"] = c["warp_inst_executed_per_launch"]
+                e["issue_frac"] = c["warp_inst_executed_per_launch"] / (avg * 1e-3) / issue_peak if avg > 0 else None
+                e["ncu"] = {k: c[k] for k in ("issue_active_pct", "l1tex_data_pipe_wavefronts_pct") if k in c}
+                e["ncu"]["source"] = cap.get("_file")
         else:
             e["bound"] = "hbm"
+            if c and name == "sort":
+                e["ncu"] = {"per_pass": c, "source": cap.get("_file")}
         out[name] = e
     for e in out.values():
         e["share"] = e["ms"] / total if total > 0 else None
-    return out, {"P": P, "V": V, "L": int(L), "sum_n_contrib": pairs, "tiles": tiles, "sort_passes": passes}
+    return out, {"P": P, "V": V, "L": int(L), "sum_n_contrib": pairs, "tiles": tiles, "sort_passes_ref": passes,
+                 "sort_passes_own": f"4 over P + {tile_passes} over L"}
 
 
 def ref_cuda_views_per_sec(torch, wl, n_views):
@@ -560,28 +593,24 @@ def run_gsr(args):
         return
     top = max(stages, key=lambda k: stages[k]["ms"])
     t = stages[top]
-    traffic, ncu = None, None  # of the dominant kernel, per launch, from the committed ncu --set full capture
-    try:
-        cap = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))[top]
-        traffic = cap["dram_bytes_per_launch"]
-        ncu = {k: cap[k] for k in ("issue_active_pct", "l1tex_data_pipe_wavefronts_pct", "warp_inst_executed_per_launch")
-               if k in cap}
-    except Exception:
-        pass
     if t["bound"] == "hbm":
         roofline = {"kernel": top, "bound": "hbm", "achieved": t["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s",
-                    "frac": t["hbm_frac"], "traffic": traffic, "peak_source": peak_src}
+                    "frac": t["hbm_frac"], "traffic": t.get("dram_bytes"), "traffic_source": t.get("dram_bytes_source"),
+                    "peak_source": peak_src}
     else:
-        fp32_peak_t = 148 * 128 * sm_max * 1e6 / 1e12
-        roofline = {"kernel": top, "bound": "fp32-issue", "achieved": t["fp32_frac"] * fp32_peak_t, "peak": fp32_peak_t,
-                    "unit": "T lane-instr/s", "frac": t["fp32_frac"], "traffic": traffic,
+        issue_peak_g = 148 * 4 * sm_max * 1e6 / 1e9
+        roofline = {"kernel": top, "bound": "issue", "unit": "G warp-instr/s", "peak": issue_peak_g,
+                    "achieved": (t["issue_frac"] * issue_peak_g) if t.get("issue_frac") else None,
+                    "frac": t.get("issue_frac"), "traffic": t.get("dram_bytes"), "traffic_source": t.get("dram_bytes_source"),
+                    "vs_reference_algorithm": t["vs_reference_algorithm"],
                     "hbm_view": {"achieved": t["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": t["hbm_frac"]},
-                    "peak_source": "148 SM x 128 FP32 lanes x sm_max_mhz; HBM " + peak_src,
-                    "note": "achieved = SURVEY 8(d) algorithmic lane-instructions of the REFERENCE algorithm (sum n_contrib x 20 fwd / "
-                            "45 bwd) / measured time; per-warp culling and the one-scalar backward recurrence execute fewer, so "
-                            "frac can exceed 1. What the kernel itself saturates is in `ncu` (issue slots, L1TEX data pipe)."}
-        if ncu:
-            roofline["ncu"] = ncu
+                    "peak_source": "148 SMs x 4 schedulers x sm_max_mhz (one warp-instruction per scheduler per clock); HBM " + peak_src,
+                    "note": "frac = warp-instructions this kernel executes per launch (ncu smsp__inst_executed.sum of the committed "
+                            "capture, traffic_source) / live CUDA-event time / issue peak.  vs_reference_algorithm = SURVEY 8(d) "
+                            "lane-instructions of the REFERENCE algorithm (sum n_contrib x 45 bwd / 20 fwd) / time / (148 x 128 "
+                            "lanes x clock): above 1 because culling and the one-scalar recurrence execute fewer instructions."}
+        if t.get("ncu"):
+            roofline["ncu"] = t["ncu"]
     c = wl.scene["cam"]
     line = {
         "metric": metric_name(wl.P, wl.W, wl.H), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

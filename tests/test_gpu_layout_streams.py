@@ -199,3 +199,45 @@ def test_two_streams_through_the_drop_in_module():
             for k in ga:
                 ok, worst = h.grad_close(ga[k].cpu().numpy(), gb[k].cpu().numpy())
                 assert ok, (k, worst)
+
+
+def test_speculative_forward_overflow_is_redone_exactly():
+    """Steady-state forwards size point_list / scratch from the previous view of the same shape and launch binning +
+    blending before the host has seen the duplicate count (gsr_forward_render_speculative).  A view whose count
+    exceeds 1.25 x the previous one overflows that capacity and must be redone with the exact size: same image,
+    same saved state, same gradients as with speculation off; a count far BELOW the capacity must work as well."""
+    import diff_gaussian_rasterization as dgr
+    from gsr_synth import look_at_camera
+    s = h.make_scene("small")
+    W, H = 320, 240
+    far, near = look_at_camera((0, 0, -9.0), width=W, height=H), look_at_camera((0, 0, -2.2), width=W, height=H)
+    dL = torch.from_numpy(np.random.default_rng(1).standard_normal((3, H, W)).astype(np.float32)).cuda()
+
+    def run(cam):
+        sc = dict(s); sc["cam"] = cam
+        t = h.scene_tensors(s)
+        m2 = torch.zeros((s["P"], 3), device="cuda", requires_grad=True)
+        img, radii = dgr.GaussianRasterizer(h.settings_for(sc))(
+            means3D=t["means3D"], means2D=m2, opacities=t["opacities"], shs=t["shs"], scales=t["scales"],
+            rotations=t["rotations"])
+        L = img.grad_fn.num_rendered
+        (img * dL).sum().backward()
+        return img.detach().clone(), L, {k: v.grad.clone() for k, v in t.items()}
+
+    old = dgr.SPECULATE
+    try:
+        dgr.SPECULATE = False
+        want = [run(c) for c in (far, near, far)]
+        assert want[1][1] > 1.25 * want[0][1] + 4096, "the near view must overflow the far view's capacity"
+        dgr.SPECULATE = True
+        dgr._states.clear()  # forget the shapes seen so far
+        got = [run(c) for c in (far, near, far)]  # not speculated / overflow + redo / capacity far above the count
+        again = [run(c) for c in (far, near, far)]  # speculated with a fitting capacity
+    finally:
+        dgr.SPECULATE = old
+    for res in (got, again):
+        for (ia, La, ga), (ib, Lb, gb) in zip(res, want):
+            assert La == Lb and torch.equal(ia, ib)
+            for k in ga:
+                ok, worst = h.grad_close(ga[k].cpu().numpy(), gb[k].cpu().numpy())
+                assert ok, (k, worst)
