@@ -52,10 +52,12 @@ def bind_host_to_gpu_numa(device) -> Optional[str]:
 
 
 class _Slot:
-    def __init__(self, n_param, n_views, H, W, dev, widths, P):
+    def __init__(self, n_param, n_views, H, W, dev, widths, P, n_alloc=None, shard=0):
         f32 = torch.float32
-        self.param = torch.empty(n_param, dtype=f32, device=dev)
-        self.grad = torch.zeros(n_param, dtype=f32, device=dev)
+        n_alloc = n_param if n_alloc is None else n_alloc  # padded so that it splits into equal per-rank slices
+        self.param = torch.empty(n_alloc, dtype=f32, device=dev)
+        self.grad = torch.zeros(n_alloc, dtype=f32, device=dev)
+        self.grad_shard = torch.empty(shard, dtype=f32, device=dev) if shard else None  # reduce-scatter output
         self.cam = torch.empty((n_views, 36), dtype=f32, device=dev)
         self.dL = torch.empty((n_views, 3, H, W), dtype=f32, device=dev)
         self.p, self.g = {}, {}
@@ -85,35 +87,52 @@ class HostStepPipeline:
         # host and device share one layout: slices[name] = (begin, end) in floats, every begin 256-byte aligned
         self.slices, self.n_param = flat_layout({n: P * w for n, w in self.widths})
         self.bg = torch.zeros(3, device=self.dev) if bg is None else bg.to(self.dev).float()
-        self.slots: List[_Slot] = [_Slot(self.n_param, n_views, H, W, self.dev, self.widths, P) for _ in range(depth)]
         self.s_in = torch.cuda.Stream(self.dev)
         self.s_out = torch.cuda.Stream(self.dev)
         self.group = group
         # With several ranks on one box every rank would pull the same 236 B/Gaussian attribute vector over PCIe and
-        # push the same all-reduced gradient back: instead rank 0 uploads the attributes once and broadcasts them over
-        # NVLink, and only rank 0 copies the (identical) gradient to the host.
+        # push the same reduced gradient back.  Instead the host traffic is SHARDED over the ranks' own PCIe links:
+        # rank r uploads slice r of the attribute vector, an all-gather over NVLink completes it on every GPU; the
+        # gradient is reduce-scattered and rank r copies slice r of the sum to its host buffer (the slices of all ranks
+        # concatenate to the full gradient: `grad_slice`).  The input all-gather runs on its own process group /
+        # communicator on the copy-in stream, so it never queues behind the gradient collective of the previous step.
         self.world, self.rank = 1, 0
         if group is not False:
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized():
                 self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.share = bool(share_over_nvlink) and self.world > 1
+        self.in_group = None
+        if self.share:
+            import torch.distributed as dist
+            ranks = dist.get_process_group_ranks(group) if group is not None else None
+            self.in_group = dist.new_group(ranks=ranks)  # collective: every rank of `group` constructs the pipeline
+        self.n_pad = (self.n_param + self.world - 1) // self.world * self.world  # device buffers: equal slices
+        self.shard = self.n_pad // self.world
+        lo = self.rank * self.shard
+        self.grad_slice = (lo, min(lo + self.shard, self.n_param)) if self.share else (0, self.n_param)
+        self.slots: List[_Slot] = [_Slot(self.n_param, n_views, H, W, self.dev, self.widths, P, n_alloc=self.n_pad,
+                                         shard=self.shard if self.share else 0) for _ in range(depth)]
         self.views = _views.ViewPipeline(self.dev, overlap=overlap)
         self.n_submitted = 0
         self.staged = None  # slot whose inputs are in flight and whose compute has not been issued yet
-        self.h2d_bytes = 4 * (self.n_param + n_views * 36 + n_views * 3 * H * W)  # rank 0; others skip n_param if shared
-        self.d2h_bytes = 4 * self.n_param                                         # rank 0
+        n_io = (self.grad_slice[1] - self.grad_slice[0])
+        self.h2d_bytes = 4 * (n_io + n_views * 36 + n_views * 3 * H * W)  # per rank
+        self.d2h_bytes = 4 * n_io                                         # per rank
 
     # -- stages ---------------------------------------------------------------------------------------------
     def _copy_in(self, slot, host_param, host_cam, host_dL):
         with torch.cuda.stream(self.s_in):
             if slot.used:
                 self.s_in.wait_event(slot.ev_compute)  # the previous step in this slot has finished reading
-            if not self.share or self.rank == 0:
-                slot.param.copy_(host_param, non_blocking=True)
-            if self.share:
+            if not self.share:
+                slot.param[:self.n_param].copy_(host_param, non_blocking=True)
+            else:
                 import torch.distributed as dist
-                dist.broadcast(slot.param, src=dist.get_global_rank(self.group, 0) if self.group else 0, group=self.group)
+                lo, hi = self.grad_slice
+                mine = slot.param[self.rank * self.shard:(self.rank + 1) * self.shard]
+                mine[:hi - lo].copy_(host_param[lo:hi], non_blocking=True)  # this rank's slice over its own PCIe link
+                dist.all_gather_into_tensor(slot.param, mine, group=self.in_group)  # in place, over NVLink
             slot.cam.copy_(host_cam, non_blocking=True)
             slot.dL.copy_(host_dL, non_blocking=True)
             slot.ev_in.record(self.s_in)
@@ -134,17 +153,22 @@ class HostStepPipeline:
                 sh_degree=self.sh_degree, campos=cm[32:35], prefiltered=False, debug=False))
         self.views.step(settings, lambda img, k: slot.dL[k], slot.g, p["means3D"], p["opacities"], shs=p["shs"],
                         scales=p["scales"], rotations=p["rotations"])
-        if self.group is not False:
+        if self.world > 1:
             import torch.distributed as dist
-            if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            if self.share:  # rank r keeps slice r of the sum
+                dist.reduce_scatter_tensor(slot.grad_shard, slot.grad, group=self.group)
+            else:
                 dist.all_reduce(slot.grad, group=self.group)
         slot.ev_compute.record(cur)
 
     def _copy_out(self, slot, host_grad):
         with torch.cuda.stream(self.s_out):
             self.s_out.wait_event(slot.ev_compute)
-            if not self.share or self.rank == 0:
-                host_grad.copy_(slot.grad, non_blocking=True)
+            if not self.share:
+                host_grad.copy_(slot.grad[:self.n_param], non_blocking=True)
+            else:
+                lo, hi = self.grad_slice
+                host_grad[lo:hi].copy_(slot.grad_shard[:hi - lo], non_blocking=True)
             slot.ev_out.record(self.s_out)
         slot.pending_out = host_grad
         slot.used = True
@@ -154,7 +178,8 @@ class HostStepPipeline:
         """Queue one step.  All four tensors are pinned host tensors (flat params, (n_views,36) cameras,
         (n_views,3,H,W) dL/dimage, flat gradient output).  The inputs must stay unchanged, and host_grad is not
         valid, until a later submit()/flush() returns it.  Returns the list of host_grad tensors that became
-        valid during this call (steps complete in submission order)."""
+        valid during this call (steps complete in submission order).  With several ranks (share_over_nvlink) only
+        host_grad[grad_slice[0]:grad_slice[1]] is written on this rank: the ranks' slices concatenate to the sum."""
         for t, n in ((host_param, "host_param"), (host_cam, "host_cam"), (host_dL, "host_dL"), (host_grad, "host_grad")):
             if t.is_cuda or not t.is_pinned():
                 raise RuntimeError(f"{n} must be a pinned host tensor")

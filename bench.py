@@ -64,6 +64,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-drop-in", action="store_true", help="skip the drop-in autograd API measurements")
+    ap.add_argument("--no-c3", action="store_true",
+                    help="skip the extra C3 leg (BASELINE configs[2]: 3M Gaussians, 64 views per step over all ranks)")
     ap.add_argument("--cpu-sample-views", type=int, default=1)
     ap.add_argument("--stages-out", default=None, help="write the per-stage table as JSON to this file")
     return ap.parse_args()
@@ -329,11 +331,11 @@ class Workload:
         out = self.host_grad if self.e2e_i % 2 == 0 else self.host_grad2
         self.e2e_i += 1
         for g in pipe.submit(self.host_param, self.host_cam, self.host_dL, out):
-            self.e2e_read += float(g[0])
+            self.e2e_read += float(g[pipe.grad_slice[0]])  # this rank's slice of the summed gradient is on the host
 
     def finish_e2e(self):
         for g in self.pipe.flush():
-            self.e2e_read += float(g[0])
+            self.e2e_read += float(g[self.pipe.grad_slice[0]])
 
     def step_e2e(self, dist=None):
         t = self.torch
@@ -519,6 +521,38 @@ def ref_cuda_views_per_sec(torch, wl, n_views):
     return n_views / (a.elapsed_time(b) * 1e-3)
 
 
+def c3_leg(args, torch, dist, rank, world, dev, wl_c2):
+    """C3 (BASELINE configs[2]): 3M Gaussians SH3, 1920x1080, 64 views per PGD step sharded over the ranks, NCCL
+    all-reduce of the attribute gradients.  Strong scaling: the step is fixed, each rank renders 64 / N views."""
+    # release the C2 workload's device and pinned buffers first
+    for k in list(vars(wl_c2)):
+        setattr(wl_c2, k, None)
+    torch.cuda.empty_cache()
+    a3 = argparse.Namespace(**{**vars(args), "workload": "C3", "views": 64 // world, "P": None, "api": "views",
+                               "no_overlap": False, "sh_objs": False})
+    wl = Workload(a3, torch, rank, world, dev)
+    steps = 2
+    ms = timed(torch, dist, lambda: wl.step(dist), steps, 1, dev)
+    out = {"metric": metric_name(wl.P, wl.W, wl.H), "unit": UNIT, "value": 64 * steps / (ms * 1e-3), "ms_per_step": ms / steps,
+           "steps": steps, "warmup": 1, "views_per_step": 64, "views_per_rank": 64 // world, "scaling": "strong",
+           "bucket_bytes": int(wl.flat_grad.numel() * 4)}
+    ms_e = timed(torch, dist, lambda: wl.step_e2e_pipelined(dist), steps, 1, dev, finish=wl.finish_e2e)
+    per_view_in = wl.pipe.h2d_bytes - 4 * (wl.pipe.grad_slice[1] - wl.pipe.grad_slice[0])
+    out["e2e"] = {"value": 64 * steps / (ms_e * 1e-3), "unit": UNIT, "ms_per_step": ms_e / steps,
+                  "h2d_bytes_per_step": int(4 * wl.pipe.n_param + world * per_view_in),
+                  "d2h_bytes_per_step": int(4 * wl.pipe.n_param)}
+    if dist is not None:
+        reps = 5
+        ms_ar = timed(torch, dist, lambda: dist.all_reduce(wl.flat_grad), reps, 2, dev) / reps
+        nbytes = wl.flat_grad.numel() * 4
+        out["all_reduce"] = {"ms": ms_ar, "bytes": int(nbytes),
+                             "bus_gbs": 2 * (world - 1) / world * nbytes / (ms_ar * 1e-3) / 1e9}
+    for k in list(vars(wl)):
+        setattr(wl, k, None)
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_gsr(args):
     import torch
     rank = int(os.environ.get("RANK", "0"))
@@ -559,12 +593,18 @@ def run_gsr(args):
         ms_s = timed(torch, dist, lambda: wl.step_e2e(dist), max(2, args.steps // 4), 1, dev) / max(2, args.steps // 4)
         ms_e = timed(torch, dist, lambda: wl.step_e2e_pipelined(dist), args.steps, max(2, args.warmup - 1), dev,
                      finish=wl.finish_e2e)
-        e2e = {"value": views_total / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(wl.pipe.h2d_bytes),
-               "d2h_bytes_per_step": int(wl.pipe.d2h_bytes), "ms_per_step": ms_e / args.steps,
+        per_view_in = wl.pipe.h2d_bytes - 4 * (wl.pipe.grad_slice[1] - wl.pipe.grad_slice[0])  # cameras + dL/dimage of a rank
+        e2e = {"value": views_total / (ms_e * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(4 * wl.pipe.n_param + world * per_view_in),  # whole job: attributes once + every rank's views
+               "d2h_bytes_per_step": int(4 * wl.pipe.n_param),                        # whole job: the summed gradient once
+               "per_rank": {"h2d_bytes_per_step": int(wl.pipe.h2d_bytes), "d2h_bytes_per_step": int(wl.pipe.d2h_bytes)},
+               "ms_per_step": ms_e / args.steps,
                "how": "pipeline.HostStepPipeline depth 2: H2D of step i+1 and D2H of step i-1 overlap the compute of "
                       "step i; all copies, the pipeline fill and the drain are inside the timed region"
-                      + ("; with N > 1 rank 0 uploads the attribute vector once and broadcasts it over NVLink, every rank uploads "
-                         "its own cameras and dL/dimage, rank 0 reads the all-reduced gradient back" if world > 1 else ""),
+                      + ("; with N > 1 rank r uploads slice r of the attribute vector over its own PCIe link and an all-gather over "
+                         "NVLink (own communicator, copy-in stream) completes it on every GPU, every rank uploads its own cameras "
+                         "and dL/dimage, the gradient is reduce-scattered and rank r reads slice r of the sum back to its host "
+                         "buffer" if world > 1 else ""),
                "host_cpus": numa_cpus,
                "serial": {"value": world * len(wl.cams) / (ms_s * 1e-3), "unit": UNIT, "ms_per_step": ms_s,
                           "how": "same step, copies and compute on one stream, nothing overlapped"}}
@@ -587,7 +627,13 @@ def run_gsr(args):
     stages, counts = stage_table(torch, wl, max(1, min(args.steps, 5)), hbm_peak, sm_max)
     if dist is not None:
         dist.barrier()
+
+    # ---- BASELINE configs[2] as a second, smaller measurement in the same line (extra.c3): one DAGGER PGD step =
+    # 64 camera views of a 3M-Gaussian scene, split over the ranks (strong scaling), one all-reduce of the 708 MB bucket
+    do_c3 = args.workload == "C2" and args.P is None and not args.no_c3 and 64 % world == 0 and args.api == "views"
     if rank != 0:
+        if do_c3:
+            c3_leg(args, torch, dist, rank, world, dev, wl)
         if dist is not None:
             dist.destroy_process_group()
         return
@@ -620,7 +666,7 @@ def run_gsr(args):
                    "views_per_rank_per_step": len(wl.cams), "parallelism": f"view-sharded x{world}, replicated Gaussians"
                    + (", NCCL all-reduce of attribute gradients per step" if world > 1 else ""),
                    "l2": "inputs larger than L2 (236 MB of attributes + 25 MB dL/dpixel per view)", **counts},
-        "e2e": e2e, "drop_in": drop_in, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "stages": stages,
+        "e2e": e2e, "drop_in": drop_in, "extra": {"c3": None}, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "stages": stages,
     }
     if not args.no_cpu_baseline and world == 1:
         steps_c = 1
@@ -634,6 +680,8 @@ def run_gsr(args):
             "same inputs, legacy default stream, incl. its per-call zero-filled tensors"}
     if args.stages_out:
         json.dump({"stages": stages, "counts": counts}, open(args.stages_out, "w"), indent=1)
+    if do_c3:  # last: it releases the C2 workload
+        line["extra"]["c3"] = c3_leg(args, torch, dist, rank, world, dev, wl)
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

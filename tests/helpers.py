@@ -91,6 +91,8 @@ def run_gsr(scene, grad=True, fetch=True, obj=None, bg=None, colors_precomp=None
     if obj is not None:
         res["objects"] = outs[2].detach().cpu().numpy()
     fn = outs[0].grad_fn
+    if fn is not None:
+        res["num_rendered"] = fn.num_rendered
     if fetch and P:
         W, H = scene["cam"]["image_width"], scene["cam"]["image_height"]
         L = fn.num_rendered

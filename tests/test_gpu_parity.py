@@ -192,13 +192,22 @@ def test_radix_sort_ignores_bits_above_end_bit():
     assert np.array_equal(ko, keys[order]) and np.array_equal(vo, vals[order])
 
 
-@pytest.mark.parametrize("name,bwd", [("C3", True), ("C4", False)])
-def test_full_size_C3_C4_against_live_reference(name, bwd):
-    """BASELINE configs[2] (3M Gaussians, 1080p, fwd+bwd) and configs[3] (6M, 3840x2160, forward only) at full size:
-    size-independent properties, and bit-identical image / radii / duplicate count against the reference CUDA when it
-    travelled (C5, L = 1.47e9, runs in tools/config_sweep.py -- profiles/r1_config_sweep.jsonl)."""
+@pytest.mark.parametrize("name,bwd", [("C3", True), ("C4", False), ("C5", True)])
+def test_full_size_C3_C4_C5_against_live_reference(name, bwd):
+    """BASELINE configs[2] (3M Gaussians, 1080p, fwd+bwd), configs[3] (6M, 3840x2160, forward only) and configs[4]
+    (dense overlap: 2M high-opacity Gaussians with large radii, L = 1.47e9 (tile, Gaussian) pairs -- the only place
+    the sort's 64-bit look-back words (n >= 2^30) and multi-GB scratch run) at full size: size-independent properties,
+    and bit-identical image / radii / duplicate count against the reference CUDA when it travelled."""
     s = h.make_scene(name)
     g = h.run_gsr(s, grad=bwd, fetch=False)
+    if name == "C5":
+        import diff_gaussian_rasterization as dgr
+        from diff_gaussian_rasterization import _abi
+        L = g["num_rendered"]
+        assert L >= 1 << 30, L
+        need = _abi.lib().gsr_scratch_bytes(s["P"], L, 1920, 1080)
+        assert 12 * L < need < 40 * L  # three u32 arrays of L + look-back words, not the reference's 24+ B/pair + CUB temp
+        assert dgr._state(torch.device("cuda", torch.cuda.current_device())).scratch.numel() >= need
     assert np.isfinite(g["color"]).all() and g["color"].min() >= 0.0
     assert (g["radii"] >= 0).all() and (g["radii"] > 0).sum() > s["P"] // 4
     if bwd:
@@ -207,7 +216,11 @@ def test_full_size_C3_C4_against_live_reference(name, bwd):
         hidden = g["radii"] == 0
         assert not g["grads"]["sh"].reshape(s["P"], -1)[hidden].any()  # unrendered Gaussians get exact zeros
     if h.ref_available():
+        import diff_gaussian_rasterization as dgr
+        dgr._states.clear()  # give the scratch back before the reference allocates its own
+        torch.cuda.empty_cache()
         r = h.run_ref(s, grad=bwd, fetch=False)
+        assert g.get("num_rendered", r["num_rendered"]) == r["num_rendered"]
         assert np.array_equal(g["radii"], r["radii"])
         assert np.array_equal(g["color"].view(np.uint32), r["color"].view(np.uint32))
         if bwd:
