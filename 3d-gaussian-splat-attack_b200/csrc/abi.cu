@@ -6,6 +6,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
+#include <mutex>
+#include <nvtx3/nvToolsExt.h>
 #include "common.cuh"
 
 namespace gsr {
@@ -19,25 +22,45 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-// ---- profiling state (process-wide; guarded by the caller's GIL / single host thread) ----------
+// ---- NVTX ranges named after the stages (for ncu --nvtx / Nsight Systems), enabled with GSR_NVTX=1 ----
+static int nvtx_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("GSR_NVTX"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v;
+}
+void nvtx_push(int stage) {
+  static const char* names[ST_COUNT] = {"gsr:preprocess_fwd", "gsr:duplicate_keys", "gsr:sort", "gsr:tile_ranges",
+                                        "gsr:blend_fwd", "gsr:blend_bwd", "gsr:preprocess_bwd"};
+  if (nvtx_enabled() && stage >= 0 && stage < ST_COUNT) nvtxRangePushA(names[stage]);
+}
+void nvtx_pop() { if (nvtx_enabled()) nvtxRangePop(); }
+
+// ---- profiling state: process-wide, serialised by g_prof_mu (calls may come from several host threads) ----------
+static std::mutex g_prof_mu;
 static bool g_prof_on = false;
 static long long g_launches = 0;
 struct ProfRec { int stage; cudaEvent_t a, b; };
 static ProfRec g_prof[8192];
 static int g_prof_n = 0, g_prof_made = 0;
 
-void count_launches(int n) { g_launches += n; }
-void profile_begin(int stage, cudaStream_t st) {
-  if (!g_prof_on || g_prof_n >= 8192) return;
+void count_launches(int n) { __atomic_fetch_add(&g_launches, (long long)n, __ATOMIC_RELAXED); }
+bool profile_begin(int stage, cudaStream_t st) {
+  if (!g_prof_on) return false;
+  g_prof_mu.lock();  // held until profile_end: one stage is recorded at a time
+  if (g_prof_n >= 8192) return true;
   ProfRec& r = g_prof[g_prof_n];
   if (g_prof_n >= g_prof_made) { cudaEventCreate(&r.a); cudaEventCreate(&r.b); g_prof_made++; }
   r.stage = stage;
   cudaEventRecord(r.a, st);
+  return true;
 }
-void profile_end(int stage, cudaStream_t st) {
-  if (!g_prof_on || g_prof_n >= 8192) return;
-  cudaEventRecord(g_prof[g_prof_n].b, st);
-  g_prof_n++;
+void profile_end(bool recording, cudaStream_t st) {
+  if (!recording) return;
+  if (g_prof_n < 8192) {
+    cudaEventRecord(g_prof[g_prof_n].b, st);
+    g_prof_n++;
+  }
+  g_prof_mu.unlock();
 }
 
 static inline bool misaligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; }

@@ -274,13 +274,15 @@ int blend_bwd_stats(uint64_t* out_host, int reset);
 // and a count of kernel launches (gsr_launch_count) ------------------------------------------------
 enum Stage { ST_PREPROCESS_FWD = 0, ST_DUPLICATE, ST_SORT, ST_RANGES, ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD,
              ST_COUNT };
-void profile_begin(int stage, cudaStream_t st);
-void profile_end(int stage, cudaStream_t st);
+bool profile_begin(int stage, cudaStream_t st);  // true: a record is open (and the profiling lock held) until profile_end
+void profile_end(bool recording, cudaStream_t st);
 void count_launches(int n);
+void nvtx_push(int stage);  // NVTX range around the host-side launches of a stage (GSR_NVTX=1; abi.cu)
+void nvtx_pop();
 struct StageScope {
-  int stage; cudaStream_t st;
-  StageScope(int s, cudaStream_t t) : stage(s), st(t) { profile_begin(stage, st); }
-  ~StageScope() { profile_end(stage, st); }
+  int stage; cudaStream_t st; bool rec;
+  StageScope(int s, cudaStream_t t) : stage(s), st(t) { nvtx_push(stage); rec = profile_begin(stage, st); }
+  ~StageScope() { profile_end(rec, st); nvtx_pop(); }
 };
 
 }  // namespace gsr
