@@ -110,7 +110,7 @@ constexpr int SORT_ITEMS_SMALL = GSR_SORT_ITEMS_SMALL;  // 2048 pairs per block 
 constexpr int64_t SORT_SMALL_TILE_LIMIT = (int64_t)1 << 22;
 constexpr int64_t SORT_SMALL_LIMIT = (int64_t)1 << 30;  // below: 32-bit look-back words, above: 64-bit
 constexpr int SORT_MAX_PASSES = 8;
-constexpr int SORT_LB_GROUP = 16;  // tiles per look-back group (radix_sort.cu)
+constexpr int SORT_LB_GROUP = 8;   // tiles per look-back group (radix_sort.cu)
 inline int64_t sort_tiles(int64_t n, int items) { return (n + SORT_THREADS * items - 1) / (SORT_THREADS * items); }
 
 // Digit layout and tile size of one LSD sort (radix_sort.cu: make_sort_plan).

@@ -223,51 +223,52 @@ __device__ __forceinline__ void sort_tile(PassSmem<KeyT, ITEMS>& S, const KeyT* 
   SORT_TICK(5);
   // Two-level decoupled look-back.  All resident tiles reach this point at about the same time, so a plain chain
   // (sum predecessors until one has published an inclusive prefix) needs ~sqrt(tiles in flight / 2) dependent round
-  // trips to L2 -- measured: 10k of the 22k cycles a tile takes.  Here a tile first sums the aggregates of the tiles
-  // before it in its own group of 16 (at most two round trips), the last tile of a group publishes the group total,
-  // and the walk over earlier groups (8 per round trip) stops at the first group whose inclusive prefix is known.  A
-  // status word carries flag and value together, so no fence is needed around it; a tile only ever waits for tiles
-  // with a smaller ticket, which have started.
+  // trips to L2 -- measured: 10k of the 22k cycles a tile took.  Here a tile sums the aggregates of the tiles before it
+  // in its own group of 8, the last tile of a group publishes the group total, and the walk over earlier groups (8 per
+  // round trip) stops at the first group whose inclusive prefix is known.  A status word carries flag and value
+  // together, so no fence is needed around it; a tile only ever waits for tiles with a smaller ticket, which have
+  // started.  It runs AFTER the keys are staged and the values requested: what it waits for passes under that work.
   uint32_t excl = 0;
   {
-    constexpr int LBW = 8;
+    constexpr int LBW = SORT_LB_GROUP;  // words fetched per round trip
     const uint32_t grp = tile / SORT_LB_GROUP, first = grp * SORT_LB_GROUP;
-    for (uint32_t t0 = first; t0 < tile; t0 += LBW) {
-      W w[LBW];
-      bool ok;
-      do {
-        ok = true;
+    // both walks start with loads that depend on nothing: the aggregates of the tiles before this one in its group
+    // and the newest LBW group words travel in the same round trip
+    W a[LBW], g[LBW];
+    int64_t j = (int64_t)grp - 1;
 #pragma unroll
-        for (int k = 0; k < LBW; k++) {
-          w[k] = ST_AGG;
-          if (t0 + k < tile) w[k] = st[(size_t)(t0 + k) * 256 + tid];
-          ok = ok && (w[k] & ST_AGG) != 0;
-        }
-      } while (!ok);
+    for (int k = 0; k < LBW; k++) { a[k] = ST_AGG; if (first + k < tile) a[k] = st[(size_t)(first + k) * 256 + tid]; }
 #pragma unroll
-      for (int k = 0; k < LBW; k++) excl += (uint32_t)(w[k] & ST_MASK);
+    for (int k = 0; k < LBW; k++) { g[k] = ST_PREFIX; if (j - k >= 0) g[k] = gst[(size_t)(j - k) * 256 + tid]; }
+    while (true) {  // in-group: all predecessors must have published their aggregate
+      bool ok = true;
+#pragma unroll
+      for (int k = 0; k < LBW; k++) ok = ok && (a[k] & ST_AGG) != 0;
+      if (ok) break;
+#pragma unroll
+      for (int k = 0; k < LBW; k++) if (first + k < tile) a[k] = st[(size_t)(first + k) * 256 + tid];
     }
+#pragma unroll
+    for (int k = 0; k < LBW; k++) excl += (uint32_t)(a[k] & ST_MASK);
     SORT_TICK(7);  // in-group part, thread 0's digit only
     const bool leader = tile - first == SORT_LB_GROUP - 1;
     if (leader) gst[(size_t)grp * 256 + tid] = (grp == 0 ? ST_PREFIX : ST_AGG) | ((W)(excl + count) & ST_MASK);
     if (grp != 0) {
       uint32_t gsum = 0;
-      int64_t j = (int64_t)grp - 1;
       while (true) {
-        W w[LBW];
-#pragma unroll
-        for (int k = 0; k < LBW; k++) { w[k] = ST_PREFIX; if (j - k >= 0) w[k] = gst[(size_t)(j - k) * 256 + tid]; }
         bool done = false, stop = false;
         int adv = 0;
 #pragma unroll
         for (int k = 0; k < LBW; k++) {
           if (!done && !stop) {
-            if ((w[k] & (ST_AGG | ST_PREFIX)) == 0) stop = true;
-            else { gsum += (uint32_t)(w[k] & ST_MASK); adv = k + 1; done = (w[k] & ST_PREFIX) != 0; }
+            if ((g[k] & (ST_AGG | ST_PREFIX)) == 0) stop = true;
+            else { gsum += (uint32_t)(g[k] & ST_MASK); adv = k + 1; done = (g[k] & ST_PREFIX) != 0; }
           }
         }
         if (done) break;
         j -= adv;
+#pragma unroll
+        for (int k = 0; k < LBW; k++) { g[k] = ST_PREFIX; if (j - k >= 0) g[k] = gst[(size_t)(j - k) * 256 + tid]; }
       }
       excl += gsum;
       if (leader) gst[(size_t)grp * 256 + tid] = ST_PREFIX | ((W)(excl + count) & ST_MASK);
