@@ -61,12 +61,8 @@ struct BlendStage {
 // definite" escape depend on the entry and the tile only, so the staging thread folds them into the threshold once
 // for all eight warps: thr_cull = thr - (2e-6 * S_tile + 1e-4), or -inf for a degenerate conic (never culled);
 // S_tile bounds the term magnitudes over the whole tile, hence over every warp rectangle.
-__device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g, const float2* __restrict__ means2D,
-                                            const float4* __restrict__ conic_opacity,
-                                            const float4* __restrict__ rgb_thr, float tx0, float ty0) {
-  const float2 xy = means2D[g];
-  const float4 co = conic_opacity[g];
-  const float4 ct = rgb_thr[g];
+__device__ __forceinline__ void stage_record(BlendStage& S, int slot, const float2 xy, const float4 co, const float4 ct,
+                                             float tx0, float ty0) {
   const float ux = tx0 - xy.x, vy = ty0 - xy.y;
   const float um = fmaxf(fabsf(ux), fabsf(ux + (float)(TILE_X - 1))), vm = fmaxf(fabsf(vy), fabsf(vy + (float)(TILE_Y - 1)));
   const float s_tile = 0.5f * (co.x * um * um + co.z * vm * vm) + fabsf(co.y) * um * vm;
@@ -75,6 +71,31 @@ __device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g,
   S.a[slot] = make_float4(xy.y, xy.x, co.z, co.y);
   S.b[slot] = make_float4(co.x, thr_cull, __fdividef(-co.y, co.z), __fdividef(-co.y, co.x));
   S.c[slot] = make_float4(ct.x, ct.y, ct.z, co.w);
+}
+__device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g, const float2* __restrict__ means2D,
+                                            const float4* __restrict__ conic_opacity,
+                                            const float4* __restrict__ rgb_thr, float tx0, float ty0) {
+  stage_record(S, slot, means2D[g], conic_opacity[g], rgb_thr[g], tx0, ty0);
+}
+
+// Raw records of the NEXT batch, filled by cp.async while the current batch is evaluated (GSR_BLEND_ASYNC).
+struct RawStage {
+  float4 co[BLEND_BATCH];
+  float4 ct[BLEND_BATCH];
+  float2 xy[BLEND_BATCH];
+};
+__device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_8(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void raw_issue(RawStage& R, int slot, uint32_t g, const float2* __restrict__ means2D,
+                                          const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb_thr) {
+  cp_async_16(&R.co[slot], conic_opacity + g);
+  cp_async_16(&R.ct[slot], rgb_thr + g);
+  cp_async_8(&R.xy[slot], means2D + g);
 }
 
 // Conservative test of one list entry against a warp's pixel rectangle [x0, x0+WARP_W-1] x [y0, y0+WARP_H-1]:
