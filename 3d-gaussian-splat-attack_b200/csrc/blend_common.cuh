@@ -78,26 +78,6 @@ __device__ __forceinline__ void stage_entry(BlendStage& S, int slot, uint32_t g,
   stage_record(S, slot, means2D[g], conic_opacity[g], rgb_thr[g], tx0, ty0);
 }
 
-// Raw records of the NEXT batch, filled by cp.async while the current batch is evaluated (GSR_BLEND_ASYNC).
-struct RawStage {
-  float4 co[BLEND_BATCH];
-  float4 ct[BLEND_BATCH];
-  float2 xy[BLEND_BATCH];
-};
-__device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_8(void* smem, const void* gmem) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-__device__ __forceinline__ void raw_issue(RawStage& R, int slot, uint32_t g, const float2* __restrict__ means2D,
-                                          const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb_thr) {
-  cp_async_16(&R.co[slot], conic_opacity + g);
-  cp_async_16(&R.ct[slot], rgb_thr + g);
-  cp_async_8(&R.xy[slot], means2D + g);
-}
-
 // Conservative test of one list entry against a warp's pixel rectangle [x0, x0+WARP_W-1] x [y0, y0+WARP_H-1]:
 // returns false only if NO pixel of the rectangle can pass the per-pixel test `power >= threshold`.
 // f(u,v) = -0.5 (A u^2 + C v^2) - B u v is concave (the conic is positive definite), so its maximum over the

@@ -32,13 +32,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const float4* __restrict__ rgb_thr, const float* __restrict__ obj_feats,
                  const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                  float* __restrict__ out_color, float* __restrict__ out_objects) {
-#ifdef GSR_BLEND_ASYNC
-  constexpr bool ASYNC = K == 0;  // double-buffered staging: the next batch's gathers fly under this batch's blending
-#else
-  constexpr bool ASYNC = false;
-#endif
-  __shared__ BlendStage Sbuf[ASYNC ? 2 : 1];
-  __shared__ RawStage Rraw[ASYNC ? 1 : 1];  // (10 KB; only touched when ASYNC)
+  __shared__ BlendStage S;
   // object-identity features of the staged entries, four 16-byte words per entry (K = 16): staged with the batch, so
   // the blending loop reads them as broadcast shared loads instead of 16 global loads per contributing pair
   __shared__ float4 s_obj[K > 0 ? K / 4 : 1][K > 0 ? BLEND_BATCH : 1];
@@ -62,36 +56,18 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   uint32_t last_contributor = 0;
 
   const float tx0f = (float)(blockIdx.x * TILE_X), ty0f = (float)(blockIdx.y * TILE_Y);
-  uint32_t g_next = 0;  // ASYNC: list entry this thread stages in the batch after the one in flight
-  if (ASYNC) {
-    if (range.x + tid < range.y) raw_issue(Rraw[0], tid, point_list[range.x + tid], means2D, conic_opacity, rgb_thr);
-    if (range.x + BLEND_BATCH + tid < range.y) g_next = point_list[range.x + BLEND_BATCH + tid];
-  }
-  int parity = 0;
-  for (uint32_t base = range.x; base < range.y; base += BLEND_BATCH, todo -= BLEND_BATCH, parity ^= 1) {
-    BlendStage& S = Sbuf[ASYNC ? parity : 0];
-    if (ASYNC) {
-      // this thread's raw record of the batch has landed: turn it into the staged form, then send the next batch's
-      // gathers on their way; ONE barrier per batch (it also keeps the buffer of two batches ago from being
-      // overwritten while a warp still reads it)
-      cp_async_wait_all();
-      if (base + tid < range.y) stage_record(S, tid, Rraw[0].xy[tid], Rraw[0].co[tid], Rraw[0].ct[tid], tx0f, ty0f);
-      if (base + BLEND_BATCH + tid < range.y) raw_issue(Rraw[0], tid, g_next, means2D, conic_opacity, rgb_thr);
-      if (base + 2 * BLEND_BATCH + tid < range.y) g_next = point_list[base + 2 * BLEND_BATCH + tid];
-      if (__syncthreads_count(done) == TILE_PIX) break;
-    } else {
-      if (__syncthreads_count(done) == TILE_PIX) break;
-      if (base + tid < range.y) {
-        const uint32_t g = point_list[base + tid];
-        stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr, tx0f, ty0f);
-        if (K > 0) {
-          const float4* f = reinterpret_cast<const float4*>(obj_feats + (size_t)g * K);
+  for (uint32_t base = range.x; base < range.y; base += BLEND_BATCH, todo -= BLEND_BATCH) {
+    if (__syncthreads_count(done) == TILE_PIX) break;
+    if (base + tid < range.y) {
+      const uint32_t g = point_list[base + tid];
+      stage_entry(S, tid, g, means2D, conic_opacity, rgb_thr, tx0f, ty0f);
+      if (K > 0) {
+        const float4* f = reinterpret_cast<const float4*>(obj_feats + (size_t)g * K);
 #pragma unroll
-          for (int q = 0; q < K / 4; q++) s_obj[q][tid] = __ldg(f + q);
-        }
+        for (int q = 0; q < K / 4; q++) s_obj[q][tid] = __ldg(f + q);
       }
-      __syncthreads();
     }
+    __syncthreads();
     const int nb = min(BLEND_BATCH, todo);
     const uint32_t first = base - range.x;
     for (int r = 0; r < nb; r += 32) {
@@ -149,7 +125,6 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       __syncwarp();  // the queue is rewritten next round: votes and shuffles are not memory barriers
     }
   }
-  if (ASYNC) cp_async_wait_all();  // nothing may be in flight to shared memory when the block leaves
   if (inside) {
     const size_t HW = (size_t)W * H, pid = (size_t)py * W + px;
     final_T[pid] = T;
