@@ -160,7 +160,7 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   // order the Gaussians by (depth bits, index): 4 passes, the result lands back in (dkeys_a, geom.perm)
   { StageScope ps(ST_SORT, st);
     GSR_TRY(launch_sort_pairs_pingpong_u32(s.dkeys_a, g.perm, s.dkeys_b, s.dvals_b, in->P, nullptr,
-                                           make_sort_plan(in->P, 32, 4), s.sort_temp, false, st)); }
+                                           make_sort_plan(in->P, 32, 4), s.sort_temp, false, true, st)); }
   GSR_TRY(debug_sync(in, st, "depth_sort"));
   { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, num_rendered_dev, num_rendered_host, st)); }
   GSR_TRY(debug_sync(in, st, "sorted_scan"));
@@ -207,7 +207,7 @@ static int forward_binning_impl(const gsr_inputs* in, const void* geom, const in
       GSR_TRY(launch_duplicate_tiles(in->P, g, gx, k0, v0, hist, plan, L, st)); }
     GSR_TRY(debug_sync(in, st, "duplicate_tiles"));
     { StageScope ps(ST_SORT, st);
-      GSR_TRY(launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, L, n_dev, plan, s.sort_temp, fused_hist, st)); }
+      GSR_TRY(launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, L, n_dev, plan, s.sort_temp, fused_hist, false, st)); }
     GSR_TRY(debug_sync(in, st, "sort"));
   }
   { StageScope ps(ST_RANGES, st); GSR_TRY(launch_tile_ranges(L, n_dev, s.tkeys_a, im.ranges, gx * gy, st)); }
@@ -401,7 +401,7 @@ int gsr_sort_pairs_u32(const uint32_t* keys_in, uint32_t* keys_out, const uint32
   uint32_t* v1 = (passes & 1) ? vals_out : vtmp;
   if (keys_in != k0) GSR_CUDA_CHECK(cudaMemcpyAsync(k0, keys_in, (size_t)n_cap * 4, cudaMemcpyDeviceToDevice, st));
   if (vals_in != v0) GSR_CUDA_CHECK(cudaMemcpyAsync(v0, vals_in, (size_t)n_cap * 4, cudaMemcpyDeviceToDevice, st));
-  return launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, n_cap, n_dev, plan, st_temp, false, st);
+  return launch_sort_pairs_pingpong_u32(k0, v0, k1, v1, n_cap, n_dev, plan, st_temp, false, false, st);
 }
 
 int64_t gsr_debug_fetch(const char* name, int32_t P, int32_t W, int32_t H, int64_t L, const void* geom,

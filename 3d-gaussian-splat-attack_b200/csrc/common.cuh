@@ -247,7 +247,7 @@ int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1
                                const SortPlan& plan, void* temp, cudaStream_t st);
 int launch_sort_pairs_pingpong_u32(uint32_t* keys0, uint32_t* vals0, uint32_t* keys1, uint32_t* vals1, int64_t n_cap,
                                    const uint32_t* n_dev, const SortPlan& plan, void* temp, bool hist_ready,
-                                   cudaStream_t st);
+                                   bool iota_vals, cudaStream_t st);
 int launch_tile_ranges(int64_t L_cap, const uint32_t* n_dev, const uint32_t* tile_keys_sorted, uint2* ranges, int tiles,
                        cudaStream_t st);
 int launch_blend_fwd(const gsr_inputs& in, const Geom& g, const Image& im, const uint32_t* point_list,

@@ -297,8 +297,7 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
     g.rects[idx] = rect;
     // input of the (depth bits, index) ordering: rendered Gaussians sort by their depth bits (positive floats
     // order like unsigned integers, as in the reference's keys), the others go last
-    dkeys[idx] = touched ? __float_as_uint(depth) : 0xffffffffu;
-    g.perm[idx] = (uint32_t)idx;
+    dkeys[idx] = touched ? __float_as_uint(depth) : 0xffffffffu;  // (the sort generates the indices itself)
   }
 
 }

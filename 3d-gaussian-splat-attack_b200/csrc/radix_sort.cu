@@ -53,6 +53,10 @@ struct DigitLayout {  // digit p of a key = (key >> shift[p]) & mask[p]
   uint32_t mask[SORT_MAX_PASSES];
 };
 
+// Digit histograms of every pass from one read of the keys.  Few, long-running blocks: each block ends with one
+// global reduction per populated bin, and reductions on the same word serialise in L2 (with one block per 2048 keys
+// the 1024 bins of a 1M-key depth sort took ~370 reductions each: 15 us for a 4 MB read).  Four 16-byte loads are in
+// flight per thread.
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 sort_histogram_kernel(const KeyT* __restrict__ keys, int64_t n_cap, const uint32_t* __restrict__ n_dev, int passes,
@@ -61,45 +65,31 @@ sort_histogram_kernel(const KeyT* __restrict__ keys, int64_t n_cap, const uint32
   for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) sh[i] = 0;
   __syncthreads();
   const int64_t n = device_count(n_cap, n_dev);
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
-  // whole warps iterate together (the match below names every lane): the bound is the warp's first index
-  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i - 4 * (threadIdx.x & 31) < n; i += stride) {
-    KeyT k[4];
-    int m = 4;
-    if (i >= n) {
-      m = 0;
-      for (int j = 0; j < 4; j++) k[j] = (KeyT)0;
-    } else if (i + 3 < n) {  // the key array is 16-byte aligned (caller's buffer carving): one vector load
-      if (sizeof(KeyT) == 4) {
-        const uint4 v = *reinterpret_cast<const uint4*>(keys + i);
-        k[0] = (KeyT)v.x; k[1] = (KeyT)v.y; k[2] = (KeyT)v.z; k[3] = (KeyT)v.w;
-      } else {
+  constexpr int VEC = 16 / (int)sizeof(KeyT), UNR = 4;  // keys per 16-byte load, loads in flight
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * VEC;
+  for (int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC; i0 < n; i0 += stride * UNR) {
+    KeyT k[UNR][VEC];
+    int m[UNR];
 #pragma unroll
-        for (int j = 0; j < 4; j++) k[j] = keys[i + j];
+    for (int u = 0; u < UNR; u++) {
+      const int64_t i = i0 + u * stride;
+      m[u] = i >= n ? 0 : (i + VEC <= n ? VEC : (int)(n - i));
+      if (m[u] == VEC) {  // the key array is 16-byte aligned (caller's buffer carving)
+        const uint4 v = *reinterpret_cast<const uint4*>(keys + i);
+        if (sizeof(KeyT) == 4) { k[u][0] = (KeyT)v.x; k[u][1] = (KeyT)v.y; k[u][VEC > 2 ? 2 : 0] = (KeyT)v.z; k[u][VEC > 2 ? 3 : 1] = (KeyT)v.w; }
+        else { k[u][0] = (KeyT)(((unsigned long long)v.y << 32) | v.x); k[u][1] = (KeyT)(((unsigned long long)v.w << 32) | v.z); }
+      } else {
+        for (int j = 0; j < VEC; j++) k[u][j] = j < m[u] ? keys[i + j] : (KeyT)0;
       }
-    } else {
-      m = (int)(n - i);
-      for (int j = 0; j < 4; j++) k[j] = j < m ? keys[i + j] : (KeyT)0;
     }
     for (int p = 0; p < passes; p++) {
       const int sft = dl.shift[p];
       const uint32_t msk = dl.mask[p];
-      if (p == passes - 1 && passes > 1) {
-        // the most significant digit of real keys (exponent bits of a depth, high bits of a tile id) has a few
-        // populated bins: one atomic per group of equal digits in the warp instead of 32 on the same word (MATCH.ANY
-        // costs a trip per distinct value, so it is cheap exactly here)
-        const uint32_t lt = (1u << (threadIdx.x & 31)) - 1u;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-          const uint32_t d = j < m ? (uint32_t)(k[j] >> sft) & msk : 0xffffffffu;
-          const uint32_t peers = __match_any_sync(0xffffffffu, d);
-          if (j < m && (peers & lt) == 0) atomicAdd(&sh[p * 256 + d], (uint32_t)__popc(peers));
-        }
-      } else {
+      for (int u = 0; u < UNR; u++)
 #pragma unroll
-        for (int j = 0; j < 4; j++)
-          if (j < m) atomicAdd(&sh[p * 256 + ((uint32_t)(k[j] >> sft) & msk)], 1u);
-      }
+        for (int j = 0; j < VEC; j++)
+          if (j < m[u]) atomicAdd(&sh[p * 256 + ((uint32_t)(k[u][j] >> sft) & msk)], 1u);
     }
   }
   __syncthreads();
@@ -219,7 +209,10 @@ __device__ __forceinline__ void sort_tile(PassSmem<KeyT, ITEMS>& S, const KeyT* 
   }
   uint32_t val[ITEMS];
 #pragma unroll
-  for (int i = 0; i < ITEMS; i++) val[i] = (FULL || wbase + i * 32 < tile_n) ? vp[i * 32] : 0u;
+  for (int i = 0; i < ITEMS; i++) {
+    if (vals_in == nullptr) val[i] = (uint32_t)tile_base + wbase + i * 32;  // first pass over values 0, 1, 2, ...
+    else val[i] = (FULL || wbase + i * 32 < tile_n) ? vp[i * 32] : 0u;
+  }
   SORT_TICK(5);
   // Two-level decoupled look-back.  All resident tiles reach this point at about the same time, so a plain chain
   // (sum predecessors until one has published an inclusive prefix) needs ~sqrt(tiles in flight / 2) dependent round
@@ -392,7 +385,8 @@ SortPlan make_sort_plan(int64_t n_cap, int end_bit, int key_bytes) {
 // (passes & 1).  n_dev (optional) holds the actual pair count on the device, n_cap bounds it.
 template <typename KeyT>
 static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32_t* vals1, int64_t n_cap,
-                               const uint32_t* n_dev, const SortPlan& plan, void* temp, bool hist_ready, cudaStream_t st) {
+                               const uint32_t* n_dev, const SortPlan& plan, void* temp, bool hist_ready, bool iota_vals,
+                               cudaStream_t st) {
   const int passes = plan.passes;
   if (passes < 1 || passes > (int)sizeof(KeyT) || passes > SORT_MAX_PASSES) {
     set_error("sort: end_bit %d out of range", plan.end_bit); return GSR_ERR_INVALID;
@@ -407,7 +401,8 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
       dl.shift[p] = p < passes ? plan.shift[p] : 0;
       dl.mask[p] = p < passes ? (1u << plan.bits[p]) - 1u : 0u;
     }
-    const int hist_blocks = (int)((n_cap + 2047) / 2048 < 148 * 8 ? (n_cap + 2047) / 2048 : 148 * 8);
+    const int64_t per_block = 256 * 16;  // one sweep of a block = 256 threads x 4 loads x 4 keys
+    const int hist_blocks = (int)((n_cap + per_block - 1) / per_block < 148 * 2 ? (n_cap + per_block - 1) / per_block : 148 * 2);
     sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys0, n_cap, n_dev, passes, dl, T.hist);
     GSR_LAUNCH_CHECK("sort_histogram_kernel");
   }
@@ -419,6 +414,7 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
     const KeyT* kin = (p & 1) ? keys1 : keys0;
     KeyT* kout = (p & 1) ? keys0 : keys1;
     const uint32_t* vin = (p & 1) ? vals1 : vals0;
+    if (p == 0 && iota_vals) vin = nullptr;  // the values are the indices 0 .. n-1: generated, not read
     uint32_t* vout = (p & 1) ? vals0 : vals1;
     char* stp = (char*)T.status + (size_t)p * T.pass_stride;
     const uint32_t mask = (1u << plan.bits[p]) - 1u;
@@ -434,11 +430,12 @@ static int sort_pairs_pingpong(KeyT* keys0, uint32_t* vals0, KeyT* keys1, uint32
 
 int launch_sort_pairs_pingpong(uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, int64_t n,
                                const SortPlan& plan, void* temp, cudaStream_t st) {
-  return sort_pairs_pingpong<uint64_t>(keys0, vals0, keys1, vals1, n, nullptr, plan, temp, false, st);
+  return sort_pairs_pingpong<uint64_t>(keys0, vals0, keys1, vals1, n, nullptr, plan, temp, false, false, st);
 }
 int launch_sort_pairs_pingpong_u32(uint32_t* keys0, uint32_t* vals0, uint32_t* keys1, uint32_t* vals1, int64_t n_cap,
-                                   const uint32_t* n_dev, const SortPlan& plan, void* temp, bool hist_ready, cudaStream_t st) {
-  return sort_pairs_pingpong<uint32_t>(keys0, vals0, keys1, vals1, n_cap, n_dev, plan, temp, hist_ready, st);
+                                   const uint32_t* n_dev, const SortPlan& plan, void* temp, bool hist_ready, bool iota_vals,
+                                   cudaStream_t st) {
+  return sort_pairs_pingpong<uint32_t>(keys0, vals0, keys1, vals1, n_cap, n_dev, plan, temp, hist_ready, iota_vals, st);
 }
 
 // Zeroes the sort's temp block and returns where the producer of the keys must accumulate the digit
