@@ -42,8 +42,8 @@ constexpr int NWARP = TILE_PIX / 32;
 
 struct BwdWarp {
   float2 panel[GRP][PANEL_STRIDE];  // [group slot][pixel lane] = (alpha*T, G*dL/dalpha); 0 when the pair does not contribute
-  float2 pix_rg[32];                // dL/dpixel (r, g) and (b) of each pixel lane: an 8-byte + a 4-byte read cost 3
-  float pix_b[32];                  // wavefronts where one 16-byte read with four distinct addresses costs 4
+  float2 pix_rg[32];                // dL/dpixel (r, g) and (b, 1) of each pixel lane as two 8-byte words: operand pairs of
+  float2 pix_b1[32];                // the sweep's packed FFMA2s (one 16-byte read with four distinct addresses costs more)
 };
 struct BwdSmem {
   BlendStage S;
@@ -98,19 +98,19 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
   }
   const float2* row = &Wp.panel[e][h * GRP];
   const float2* pix_rg = &Wp.pix_rg[h * GRP];
-  const float* pix_b = &Wp.pix_b[h * GRP];
+  const float2* pix_b1 = &Wp.pix_b1[h * GRP];
   // raw moments of w in the lane's local pixel coordinates (lx = 0..7, r = row inside the lane's strip): the
-  // coordinates are compile-time constants, so each sum is one FFMA/FADD per pixel (none where the factor is 0)
+  // coordinates are compile-time constants, so each sum is one FFMA/FADD per pixel (none where the factor is 0);
+  // (s0, s1) += wc (dL/dr, dL/dg) and (s2, M0) += (wc, w) (dL/db, 1) are one FFMA2 each
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, M0 = 0.f, Mx = 0.f, My = 0.f, Mxx = 0.f, Mxy = 0.f;
 #pragma unroll
   for (int i = 0; i < GRP; i++) {
     const float2 pr = row[i];
     const float2 rg = pix_rg[i];
-    const float4 dp = make_float4(rg.x, rg.y, pix_b[i], 0.f);
+    const float2 b1 = pix_b1[i];
     const int lx = i & 7, r = i >> 3;
-    fpx::fma2_bcast(s0, s1, dp.x, dp.y, pr.x);  // (s0, s1) += wc * (dL/dr, dL/dg): one FFMA2
-    s2 = fmaf(pr.x, dp.z, s2);
-    M0 += pr.y;
+    fpx::fma2_bcast(s0, s1, rg.x, rg.y, pr.x);
+    fpx::fma2_pair(s2, M0, pr.x, pr.y, b1.x, b1.y);
     if (lx == 1) { Mx += pr.y; Mxx += pr.y; }
     if (lx > 1) { Mx = fmaf(pr.y, (float)lx, Mx); Mxx = fmaf(pr.y, (float)(lx * lx), Mxx); }
     if (r == 1) {
@@ -127,12 +127,15 @@ __device__ __forceinline__ void flush_group(BwdSmem& M, BwdWarp& Wp, int ng, int
   float mxy = fmaf(Dy, a1, fmaf(-Dx, My, Mxy));                          // Dx Dy M0 - Dy Mx - Dx My + Mxy
   float myy = fmaf(Dy, a2, fmaf(-Dy, My, My));                           // Dy^2 M0 - 2 Dy My + Myy (Myy = My)
 #pragma unroll
-  for (int off = GRP; off < 32; off <<= 1) {
-    s0 += __shfl_xor_sync(0xffffffffu, s0, off); s1 += __shfl_xor_sync(0xffffffffu, s1, off);
-    s2 += __shfl_xor_sync(0xffffffffu, s2, off); m0 += __shfl_xor_sync(0xffffffffu, m0, off);
-    m1 += __shfl_xor_sync(0xffffffffu, m1, off); m2 += __shfl_xor_sync(0xffffffffu, m2, off);
-    mxx += __shfl_xor_sync(0xffffffffu, mxx, off); mxy += __shfl_xor_sync(0xffffffffu, mxy, off);
-    myy += __shfl_xor_sync(0xffffffffu, myy, off);
+  for (int off = GRP; off < 32; off <<= 1) {  // join the row strips: nine shuffles, five (packed) additions per level
+    const float t0 = __shfl_xor_sync(0xffffffffu, s0, off), t1 = __shfl_xor_sync(0xffffffffu, s1, off);
+    const float t2 = __shfl_xor_sync(0xffffffffu, s2, off), t3 = __shfl_xor_sync(0xffffffffu, m0, off);
+    const float t4 = __shfl_xor_sync(0xffffffffu, m1, off), t5 = __shfl_xor_sync(0xffffffffu, m2, off);
+    const float t6 = __shfl_xor_sync(0xffffffffu, mxx, off), t7 = __shfl_xor_sync(0xffffffffu, mxy, off);
+    const float t8 = __shfl_xor_sync(0xffffffffu, myy, off);
+    fpx::add2(s0, s1, s0, s1, t0, t1); fpx::add2(s2, m0, s2, m0, t2, t3);
+    fpx::add2(m1, m2, m1, m2, t4, t5); fpx::add2(mxx, mxy, mxx, mxy, t6, t7);
+    myy += t8;
   }
   if (lane < ng) {
     float* dst = accum + (size_t)g * 12;  // 48-byte rows: two 16-byte vector reductions + one scalar
@@ -172,7 +175,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   float dpix[3] = {0.f, 0.f, 0.f};
   if (inside) { dpix[0] = dL_dpix[pid]; dpix[1] = dL_dpix[HW + pid]; dpix[2] = dL_dpix[2 * HW + pid]; }
   Wp.pix_rg[lane] = make_float2(dpix[0], dpix[1]);
-  Wp.pix_b[lane] = dpix[2];
+  Wp.pix_b1[lane] = make_float2(dpix[2], 1.0f);
   float dpo[K > 0 ? K : 1];
 #pragma unroll
   for (int k = 0; k < (K > 0 ? K : 1); k++) dpo[k] = (K > 0 && inside) ? dL_dobjpix[k * HW + pid] : 0.f;

@@ -87,6 +87,15 @@ __device__ __forceinline__ void mul2(float& r0, float& r1, float a0, float a1, f
       "mul.rn.f32x2 c, a, b;\n\t"
       "mov.b64 {%0, %1}, c; }" : "=f"(r0), "=f"(r1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
 }
+// (lo, hi) <- (a0, a1) * (b0, b1) + (lo, hi)
+__device__ __forceinline__ void fma2_pair(float& lo, float& hi, float a0, float a1, float b0, float b1) {
+  asm("{ .reg .b64 a, b, c;\n\t"
+      "mov.b64 a, {%2, %3};\n\t"
+      "mov.b64 b, {%4, %5};\n\t"
+      "mov.b64 c, {%0, %1};\n\t"
+      "fma.rn.f32x2 c, a, b, c;\n\t"
+      "mov.b64 {%0, %1}, c; }" : "+f"(lo), "+f"(hi) : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
 // (r0, r1) <- (a0, a1) * w
 __device__ __forceinline__ void mul2_bcast(float& r0, float& r1, float a0, float a1, float w) {
   asm("{ .reg .b64 a, b, c;\n\t"
