@@ -137,7 +137,7 @@ int gsr_debug_sort_profile(uint64_t* out_host, int reset) {
   return sort_profile_read(out_host, reset);
 }
 
-size_t gsr_geom_bytes(int32_t P) { return Geom(nullptr, P).bytes; }
+size_t gsr_geom_bytes(int32_t P) { return P <= 0 ? 0 : Geom(nullptr, P).bytes; }
 size_t gsr_image_bytes(int32_t W, int32_t H) { return Image(nullptr, W, H).bytes; }
 size_t gsr_scratch_bytes(int32_t P, int64_t L_cap, int32_t, int32_t) { return Scratch(nullptr, P, L_cap).bytes; }
 size_t gsr_sort_temp_bytes(int64_t n) { return sort_temp_bytes(n, 64, 8) + align_up((size_t)n * 8) + align_up((size_t)n * 4); }

@@ -13,6 +13,7 @@ namespace {
 
 constexpr int DUP_THREADS = 256;
 constexpr uint32_t DUP_SOLO_MAX = 6;  // rects up to this many tiles are written by their own lane
+constexpr uint32_t DUP_MED_MAX = 32;  // up to this many: four rects at a time, a quarter warp each; above: the whole warp
 
 __device__ __forceinline__ unsigned long long pack_status(uint32_t flag, uint32_t v) {
   return ((unsigned long long)flag << 32) | v;
@@ -24,7 +25,9 @@ __device__ __forceinline__ unsigned long long pack_status(uint32_t flag, uint32_
 __global__ void __launch_bounds__(256)
 scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ tiles_touched,
                   uint32_t* __restrict__ offsets, unsigned long long* status, uint32_t* ticket,
-                  uint32_t* __restrict__ total_out, volatile uint32_t* total_host, int nblocks) {
+                  uint32_t* __restrict__ total_out, volatile uint32_t* total_host, int nblocks,
+                  uint32_t* __restrict__ giant_count, uint4* __restrict__ giants, uint32_t* __restrict__ giants_w,
+                  const ushort4* __restrict__ rects) {
   __shared__ uint32_t s_tile, s_warp[8], s_prefix;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);  // blocks are numbered in start order -> look-back cannot deadlock
@@ -44,6 +47,9 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __re
 #pragma unroll
     for (int k = 0; k < 4; k++) v[k] = base + k < P ? tiles_touched[perm ? perm[base + k] : (uint32_t)(base + k)] : 0u;
   }
+  uint32_t raw[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) raw[k] = v[k];
 #pragma unroll
   for (int k = 0; k < 4; k++) { sum += v[k]; v[k] = sum; }
   uint32_t incl = sum;
@@ -99,6 +105,19 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __re
   }
   __syncthreads();
   const uint32_t off = s_prefix + (warp ? s_warp[warp - 1] : 0u) + (incl - sum);
+  if (giants) {  // complete records of the rects that all blocks of the emission kernel expand together
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      if (raw[k] > GIANT_TILES) {
+        const uint32_t slot = atomicAdd(giant_count, 1u);
+        if (slot < (uint32_t)GIANT_CAP) {
+          const uint32_t gid = perm[base + k];
+          const ushort4 r = rects[gid];
+          giants[slot] = make_uint4(gid, off + v[k] - raw[k], raw[k], (uint32_t)r.x | ((uint32_t)r.y << 16));
+          giants_w[slot] = (uint32_t)r.z - r.x;
+        }
+      }
+  }
   if (base + 3 < P) {
     *reinterpret_cast<uint4*>(offsets + base) = make_uint4(off + v[0], off + v[1], off + v[2], off + v[3]);
   } else {
@@ -107,16 +126,18 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __re
   }
 }
 
-// Emits the (tile id, Gaussian) pairs in depth order.  One lane per Gaussian for small rects; rects larger than
-// DUP_SOLO_MAX are expanded by the whole warp (coalesced 32-wide stores), which removes the reference's load
-// imbalance on large splats.  Tiles of one Gaussian are emitted in row-major order, as the reference does.
+// Emits the (tile id, Gaussian) pairs in depth order.  One lane per Gaussian for small rects (<= 6 tiles), four
+// medium rects (<= 32 tiles: 40 % of the pairs of C2, 43 % of C4) at a time on a quarter warp each, larger ones
+// expanded by the whole warp (coalesced 32-wide stores): no load imbalance on large splats as in the reference.  Tiles of one Gaussian are emitted in row-major order, as the reference does.
 // Blocks stride over 256-Gaussian chunks and also build the digit histograms of the tile-id sort that follows
 // (hist[p * 256 + digit of pass p]), so that sort needs no histogram pass of its own.
 __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets_sorted,
                        const uint32_t* __restrict__ tiles_touched, const ushort4* __restrict__ rects, int gx,
                        uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ hist,
-                       uint32_t mask0, int shift1, uint32_t mask1, uint32_t cap) {
+                       uint32_t mask0, int shift1, uint32_t mask1, uint32_t cap,
+                       const uint32_t* __restrict__ giant_count, const uint4* __restrict__ giants,
+                       const uint32_t* __restrict__ giants_w) {
   // hist != nullptr: the tile sort has at most two digits, (key & mask0) and ((key >> shift1) & mask1), both
   // <= 8 bits wide (launch_duplicate_tiles): sh[] has two 256-bin rows.  Pairs beyond `cap` (the capacity of a
   // speculative launch that was sized before the count was known) are neither written nor counted.
@@ -124,6 +145,20 @@ duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t*
   for (int k = threadIdx.x; k < 2 * 256; k += DUP_THREADS) sh[k] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31;
+  auto emit = [&](uint32_t pos, uint32_t key, uint32_t gid) {
+    if (pos < cap) {
+      keys[pos] = key;
+      vals[pos] = gid;
+      if (hist) {
+        atomicAdd(&sh[key & mask0], 1u);
+        atomicAdd(&sh[256 + ((key >> shift1) & mask1)], 1u);
+      }
+    }
+  };
+  // rects above GIANT_TILES were listed by the scan: they are left out of the per-warp paths below and expanded by
+  // all blocks together at the end (unless the list overflowed: then every rect is handled where it is met)
+  const uint32_t n_giants = __ldg(giant_count);
+  const uint32_t giant_min = n_giants <= (uint32_t)GIANT_CAP ? GIANT_TILES : 0xffffffffu;
   const int nchunks = (P + DUP_THREADS - 1) / DUP_THREADS;
   for (int chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
     const int i = chunk * DUP_THREADS + threadIdx.x;
@@ -140,36 +175,60 @@ duplicate_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t*
     if (area > 0 && area <= DUP_SOLO_MAX) {
       uint32_t x = 0, y = 0;
       for (uint32_t t = 0; t < area; t++) {
-        const uint32_t key = (y0 + y) * gx + x0 + x;
-        if (off + t < cap) {
-          keys[off + t] = key;
-          vals[off + t] = id;
-          if (hist) {
-            atomicAdd(&sh[key & mask0], 1u);
-            atomicAdd(&sh[256 + ((key >> shift1) & mask1)], 1u);
-          }
-        }
+        emit(off + t, (y0 + y) * gx + x0 + x, id);
         if (++x == w) { x = 0; y++; }
       }
     }
-    uint32_t big = __ballot_sync(0xffffffffu, area > DUP_SOLO_MAX);
+    // medium rects (DUP_SOLO_MAX < area <= DUP_MED_MAX): four at a time, each expanded by a quarter warp
+    uint32_t med = __ballot_sync(0xffffffffu, area > DUP_SOLO_MAX && area <= DUP_MED_MAX);
+    const int sub = lane >> 3, sl = lane & 7;
+    while (med) {
+      // the sub-th lowest set bit of `med` is this quarter's Gaussian (none left: src = -1)
+      uint32_t m = med;
+      int src = -1;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int f = __ffs(m) - 1;
+        if (q == sub) src = f;
+        m &= m - 1;
+      }
+      med = m;
+      const int s0 = src < 0 ? 0 : src;
+      const uint32_t a_src = __shfl_sync(0xffffffffu, area, s0), o = __shfl_sync(0xffffffffu, off, s0);
+      const uint32_t a = src < 0 ? 0u : a_src;
+      const uint32_t bx = __shfl_sync(0xffffffffu, x0, s0), by = __shfl_sync(0xffffffffu, y0, s0);
+      const uint32_t bw = __shfl_sync(0xffffffffu, w, s0), bid = __shfl_sync(0xffffffffu, id, s0);
+      const float rw = 1.0f / (float)bw;
+      const uint32_t amax = __reduce_max_sync(0xffffffffu, a);
+      for (uint32_t t0 = 0; t0 < amax; t0 += 8) {
+        const uint32_t t = t0 + sl;
+        const uint32_t y = (uint32_t)(((float)t + 0.5f) * rw), x = t - y * bw;  // exact: t, bw <= 32
+        if (t < a) emit(o + t, (by + y) * gx + bx + x, bid);
+      }
+    }
+    // large rects: the whole warp expands one at a time (coalesced 32-wide stores)
+    uint32_t big = __ballot_sync(0xffffffffu, area > DUP_MED_MAX && area <= giant_min);
     while (big) {
       const int src = __ffs(big) - 1;
       big &= big - 1;
       const uint32_t a = __shfl_sync(0xffffffffu, area, src), o = __shfl_sync(0xffffffffu, off, src);
       const uint32_t bx = __shfl_sync(0xffffffffu, x0, src), by = __shfl_sync(0xffffffffu, y0, src);
       const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bid = __shfl_sync(0xffffffffu, id, src);
-      for (uint32_t t = lane; t < a; t += 32) {
+      for (uint32_t t0 = 0; t0 < a; t0 += 32) {
+        const uint32_t t = t0 + lane;
         const uint32_t y = t / bw, x = t - y * bw;
-        const uint32_t key = (by + y) * gx + bx + x;
-        if (o + t < cap) {
-          keys[o + t] = key;
-          vals[o + t] = bid;
-          if (hist) {
-            atomicAdd(&sh[key & mask0], 1u);
-            atomicAdd(&sh[256 + ((key >> shift1) & mask1)], 1u);
-          }
-        }
+        if (t < a) emit(o + t, (by + y) * gx + bx + x, bid);
+      }
+    }
+  }
+  if (giant_min != 0xffffffffu) {
+    // one listed rect per block at a time, expanded by all 256 threads (coalesced stores)
+    for (uint32_t gi = blockIdx.x; gi < n_giants; gi += gridDim.x) {
+      const uint4 rec = giants[gi];  // (Gaussian, first output slot, tiles, x0 | y0 << 16)
+      const uint32_t bw = giants_w[gi], bx = rec.w & 0xffffu, by = rec.w >> 16;
+      for (uint32_t t = threadIdx.x; t < rec.z; t += DUP_THREADS) {
+        const uint32_t y = t / bw, x = t - y * bw;
+        emit(rec.y + t, (by + y) * gx + bx + x, rec.x);
       }
     }
   }
@@ -227,7 +286,8 @@ int launch_sorted_scan(int P, const Geom& g, Scratch& s, uint32_t* num_rendered_
                        cudaStream_t st) {
   const int nb = (P + SCAN_ITEMS - 1) / SCAN_ITEMS;
   scan_tiles_kernel<<<nb, 256, 0, st>>>(P, g.perm, g.tiles_touched, g.offsets_sorted, s.scan2_status, s.scan_ticket + 1,
-                                        num_rendered_dev, num_rendered_host, nb);
+                                        num_rendered_dev, num_rendered_host, nb, g.giant_count, g.giants, g.giants_w,
+                                        g.rects);
   GSR_LAUNCH_CHECK("scan_tiles_kernel");
   return GSR_OK;
 }
@@ -237,7 +297,8 @@ int launch_index_scan(int P, const Geom& g, Scratch& s, uint32_t* out, cudaStrea
   const int nb = (P + SCAN_ITEMS - 1) / SCAN_ITEMS;
   GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_status, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
   GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_ticket, 0, sizeof(uint32_t), st));
-  scan_tiles_kernel<<<nb, 256, 0, st>>>(P, nullptr, g.tiles_touched, out, s.scan_status, s.scan_ticket, nullptr, nullptr, nb);
+  scan_tiles_kernel<<<nb, 256, 0, st>>>(P, nullptr, g.tiles_touched, out, s.scan_status, s.scan_ticket, nullptr, nullptr, nb,
+                                        nullptr, nullptr, nullptr, nullptr);
   GSR_LAUNCH_CHECK("scan_tiles_kernel");
   return GSR_OK;
 }
@@ -254,7 +315,8 @@ int launch_duplicate_tiles(int P, const Geom& g, int gx, uint32_t* tile_keys, ui
   const uint32_t mask1 = plan.passes > 1 ? (1u << plan.bits[1]) - 1u : 0u;
   const uint32_t cap32 = cap > 0xffffffffll ? 0xffffffffu : (uint32_t)cap;
   duplicate_tiles_kernel<<<blocks, DUP_THREADS, 0, st>>>(P, g.perm, g.offsets_sorted, g.tiles_touched, g.rects, gx,
-                                                         tile_keys, vals, hist, mask0, shift1, mask1, cap32);
+                                                         tile_keys, vals, hist, mask0, shift1, mask1, cap32,
+                                                         g.giant_count, g.giants, g.giants_w);
   GSR_LAUNCH_CHECK("duplicate_tiles_kernel");
   return GSR_OK;
 }

@@ -49,6 +49,16 @@ struct Carver {
   }
 };
 
+// A splat next to the camera can cover the whole image (32400 tiles at 4K): expanded by one warp, a few of them in the
+// same 256-Gaussian chunk are the tail of the whole emission kernel (C4: 0.79 ms).  Rects above GIANT_TILES are
+// listed by the scan (up to GIANT_CAP; beyond that everything is large -- the dense-overlap case -- and the work is
+// balanced anyway) and dealt to the blocks one at a time, each expanded by a whole block.
+#ifndef GSR_GIANT_TILES
+#define GSR_GIANT_TILES 512
+#endif
+constexpr uint32_t GIANT_TILES = GSR_GIANT_TILES;
+constexpr int GIANT_CAP = 16384;
+
 // Per-view geometry state (what the reference keeps in GeometryState, rasterizer_impl.h:29-44,
 // minus CUB temp, plus the tile rect and the packed blend record).
 struct Geom {
@@ -62,7 +72,10 @@ struct Geom {
   ushort4* rects;          // [P]  (x0, y0, x1, y1) tile rect (auxiliary.h:46-56)
   uint32_t* perm;          // [P]  Gaussian indices in (depth bits, index) order
   uint32_t* offsets_sorted;// [P]  inclusive prefix sum of tiles_touched[perm[.]]
-  size_t bytes;
+  uint32_t* giant_count;   // [1]  rects above GIANT_TILES (listed by the depth-order scan for the emission kernel; they
+  uint4* giants;           // [GIANT_CAP] (Gaussian, first output slot, tiles, x0 | y0 << 16)   live here, not in scratch,
+  uint32_t* giants_w;      // [GIANT_CAP] width in tiles                                       because scratch may be
+  size_t bytes;            //                                                    re-allocated between the two phases)
   Geom(void* buf, int P) {
     Carver c(buf);
     size_t n = (size_t)P;
@@ -76,6 +89,9 @@ struct Geom {
     rects = c.take<ushort4>(n);
     perm = c.take<uint32_t>(n);
     offsets_sorted = c.take<uint32_t>(n);
+    giant_count = c.take<uint32_t>(1);
+    giants = c.take<uint4>(GIANT_CAP);
+    giants_w = c.take<uint32_t>(GIANT_CAP);
     bytes = c.off;
   }
 };

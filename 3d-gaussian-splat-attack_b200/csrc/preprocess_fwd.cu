@@ -316,6 +316,7 @@ int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch
                           cudaStream_t st) {
   const int nblocks = (in.P + PRE_THREADS - 1) / PRE_THREADS;
   GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_status, 0, s.scan_zero_bytes, st));
+  GSR_CUDA_CHECK(cudaMemsetAsync(g.giant_count, 0, sizeof(uint32_t), st));
   (void)num_rendered_dev;  // written by the depth-order scan (launch_sorted_scan)
   if (in.shs_rest != nullptr || in.raw_params != 0)
     preprocess_fwd_kernel<true><<<nblocks, PRE_THREADS, 0, st>>>(in, g, radii, s.flags, s.dkeys_a);
