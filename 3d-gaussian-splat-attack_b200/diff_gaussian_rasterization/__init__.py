@@ -9,7 +9,10 @@ submodules/diff-gaussian-rasterization of poloclub/3d-gaussian-splat-attack):
   _RasterizeGaussians            (:44-155)   autograd Function, same argument / gradient order
 plus the superset that poloclub's own gaussian_renderer/__init__.py:86-95 relies on: an optional
 `sh_objs` (P,1,16) input and a third output `rendered_objects` (16,H,W) when it is given
-(Gaussian-Grouping's fork; not vendored in the reference, so that channel's parity is unpinned).
+(Gaussian-Grouping's fork; not vendored and not version-pinned in the reference, so that channel is EXPERIMENTAL: its parity
+is unpinned -- 16 extra features blended with the colour's alpha*T weights, no background term, checked against the
+oracle's restatement only).  A backward in which no gradient reaches `rendered_objects` (attack.py:485-494 reads
+render_pkg["render"] only) runs the colour-only kernels and returns None for `sh_objs`.
 
 Host logic is Python/PyTorch; all compute goes through include/gsr_b200.h via ctypes.
 There is no CPU path: non-CUDA tensors raise.
