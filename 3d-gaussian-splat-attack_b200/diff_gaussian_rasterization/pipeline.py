@@ -22,7 +22,7 @@ from . import GaussianRasterizationSettings
 from . import views as _views
 from .dist import flat_layout
 
-__all__ = ["HostStepPipeline", "ATTRS", "bind_host_to_gpu_numa"]
+__all__ = ["HostStepPipeline", "ATTRS", "bind_host_to_gpu_numa", "shard_layout"]
 
 # flat layout: name -> floats per Gaussian (SH width is 3*M, filled in per instance)
 ATTRS = ("means3D", "shs", "scales", "rotations", "opacities")
@@ -49,6 +49,19 @@ def bind_host_to_gpu_numa(device) -> Optional[str]:
         return cpulist
     except Exception:
         return None
+
+
+def shard_layout(n_param: int, world: int, rank: int):
+    """How the flat attribute / gradient vector of `n_param` floats is split over `world` ranks for host I/O:
+    returns (n_pad, shard, (lo, hi)) -- device buffers hold n_pad = world * shard elements (equal slices for
+    all_gather_into_tensor / reduce_scatter_tensor) and rank `rank` moves host elements [lo, hi) (the last slice is
+    cut at n_param).  The slices of all ranks tile [0, n_param) exactly."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError(f"bad rank/world {rank}/{world}")
+    n_pad = (n_param + world - 1) // world * world
+    shard = n_pad // world
+    lo = min(rank * shard, n_param)
+    return n_pad, shard, (lo, min(lo + shard, n_param))
 
 
 class _Slot:
@@ -107,10 +120,8 @@ class HostStepPipeline:
             import torch.distributed as dist
             ranks = dist.get_process_group_ranks(group) if group is not None else None
             self.in_group = dist.new_group(ranks=ranks)  # collective: every rank of `group` constructs the pipeline
-        self.n_pad = (self.n_param + self.world - 1) // self.world * self.world  # device buffers: equal slices
-        self.shard = self.n_pad // self.world
-        lo = self.rank * self.shard
-        self.grad_slice = (lo, min(lo + self.shard, self.n_param)) if self.share else (0, self.n_param)
+        self.n_pad, self.shard, sl = shard_layout(self.n_param, self.world, self.rank)
+        self.grad_slice = sl if self.share else (0, self.n_param)
         self.slots: List[_Slot] = [_Slot(self.n_param, n_views, H, W, self.dev, self.widths, P, n_alloc=self.n_pad,
                                          shard=self.shard if self.share else 0) for _ in range(depth)]
         self.views = _views.ViewPipeline(self.dev, overlap=overlap)

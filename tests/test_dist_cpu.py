@@ -176,3 +176,22 @@ def test_two_rank_accumulate_step_matches_autograd_reference():
     for n, p in raw.items():
         assert torch.allclose(g0[n], p.grad, rtol=1e-4, atol=1e-5), n
         assert torch.equal(g0[n], g1[n])
+
+
+def test_host_io_shard_layout_tiles_the_flat_vector():
+    """pipeline.shard_layout: the per-rank host slices of the sharded upload / read-back tile [0, n_param) exactly, the
+    padded device length splits into equal slices (all_gather_into_tensor / reduce_scatter_tensor), for any world size."""
+    from diff_gaussian_rasterization.pipeline import shard_layout
+    from diff_gaussian_rasterization.dist import flat_layout
+    for P in (1, 7, 2001, 1_000_000):
+        _, n_param = flat_layout({"means3D": 3 * P, "shs": 48 * P, "scales": 3 * P, "rotations": 4 * P, "opacities": P})
+        for world in (1, 2, 3, 4, 8):
+            seen = 0
+            for rank in range(world):
+                n_pad, shard, (lo, hi) = shard_layout(n_param, world, rank)
+                assert n_pad == shard * world and n_param <= n_pad < n_param + world
+                assert lo == seen and hi - lo <= shard
+                seen = hi
+            assert seen == n_param
+    with pytest.raises(ValueError):
+        shard_layout(10, 2, 2)
