@@ -33,25 +33,30 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __re
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);  // blocks are numbered in start order -> look-back cannot deadlock
   __syncthreads();
   const uint32_t tile = s_tile;
-  const int base = (int)tile * SCAN_ITEMS + tid * 4;
-  uint32_t v[4], sum = 0;
-  if (base + 3 < P) {
-    if (perm) {
-      const uint4 pi = *reinterpret_cast<const uint4*>(perm + base);
-      v[0] = tiles_touched[pi.x]; v[1] = tiles_touched[pi.y]; v[2] = tiles_touched[pi.z]; v[3] = tiles_touched[pi.w];
-    } else {
-      const uint4 t = *reinterpret_cast<const uint4*>(tiles_touched + base);
-      v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  constexpr int V = SCAN_ITEMS / 256;  // consecutive items per thread (a multiple of 4: 16-byte loads)
+  const int base = (int)tile * SCAN_ITEMS + tid * V;
+  uint32_t v[V], sum = 0;
+  if (base + V - 1 < P) {
+#pragma unroll
+    for (int q = 0; q < V / 4; q++) {
+      if (perm) {
+        const uint4 pi = *reinterpret_cast<const uint4*>(perm + base + 4 * q);
+        v[4 * q] = tiles_touched[pi.x]; v[4 * q + 1] = tiles_touched[pi.y];
+        v[4 * q + 2] = tiles_touched[pi.z]; v[4 * q + 3] = tiles_touched[pi.w];
+      } else {
+        const uint4 t = *reinterpret_cast<const uint4*>(tiles_touched + base + 4 * q);
+        v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+      }
     }
   } else {
 #pragma unroll
-    for (int k = 0; k < 4; k++) v[k] = base + k < P ? tiles_touched[perm ? perm[base + k] : (uint32_t)(base + k)] : 0u;
+    for (int k = 0; k < V; k++) v[k] = base + k < P ? tiles_touched[perm ? perm[base + k] : (uint32_t)(base + k)] : 0u;
   }
-  uint32_t raw[4];
+  uint32_t raw[V];
 #pragma unroll
-  for (int k = 0; k < 4; k++) raw[k] = v[k];
+  for (int k = 0; k < V; k++) raw[k] = v[k];
 #pragma unroll
-  for (int k = 0; k < 4; k++) { sum += v[k]; v[k] = sum; }
+  for (int k = 0; k < V; k++) { sum += v[k]; v[k] = sum; }
   uint32_t incl = sum;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -107,7 +112,7 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __re
   const uint32_t off = s_prefix + (warp ? s_warp[warp - 1] : 0u) + (incl - sum);
   if (giants) {  // complete records of the rects that all blocks of the emission kernel expand together
 #pragma unroll
-    for (int k = 0; k < 4; k++)
+    for (int k = 0; k < V; k++)
       if (raw[k] > GIANT_TILES) {
         const uint32_t slot = atomicAdd(giant_count, 1u);
         if (slot < (uint32_t)GIANT_CAP) {
@@ -118,11 +123,14 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __re
         }
       }
   }
-  if (base + 3 < P) {
-    *reinterpret_cast<uint4*>(offsets + base) = make_uint4(off + v[0], off + v[1], off + v[2], off + v[3]);
+  if (base + V - 1 < P) {
+#pragma unroll
+    for (int q = 0; q < V / 4; q++)
+      *reinterpret_cast<uint4*>(offsets + base + 4 * q) =
+          make_uint4(off + v[4 * q], off + v[4 * q + 1], off + v[4 * q + 2], off + v[4 * q + 3]);
   } else {
 #pragma unroll
-    for (int k = 0; k < 4; k++) if (base + k < P) offsets[base + k] = off + v[k];
+    for (int k = 0; k < V; k++) if (base + k < P) offsets[base + k] = off + v[k];
   }
 }
 

@@ -169,7 +169,10 @@ inline size_t sort_temp_bytes(int64_t n_cap, int end_bit, int key_bytes) {
 // items -- then (tile, Gaussian) pairs are emitted in that order and stably sorted by tile id alone.
 // Within a tile the result is ordered by (depth bits, index), i.e. exactly the reference's order.
 constexpr int PRE_THREADS = 256;  // Gaussians per preprocess block
-constexpr int SCAN_ITEMS = 1024;  // Gaussians per block of the sorted-order scan
+#ifndef GSR_SCAN_ITEMS
+#define GSR_SCAN_ITEMS 2048
+#endif
+constexpr int SCAN_ITEMS = GSR_SCAN_ITEMS;  // Gaussians per block of the sorted-order scan (a multiple of 1024)
 struct Scratch {
   unsigned long long* scan_status;   // [pre_blocks] look-back words of the index-order prefix sum (debug fetch only)
   unsigned long long* scan2_status;  // [scan_blocks] look-back words of the sorted-order prefix sum
