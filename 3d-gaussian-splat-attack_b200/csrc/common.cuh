@@ -123,7 +123,10 @@ constexpr int SORT_THREADS = 256;
 #endif
 constexpr int SORT_ITEMS = GSR_SORT_ITEMS;              // 4096 pairs per block
 constexpr int SORT_ITEMS_SMALL = GSR_SORT_ITEMS_SMALL;  // 2048 pairs per block for sorts of <= SORT_SMALL_TILE_LIMIT pairs
-constexpr int64_t SORT_SMALL_TILE_LIMIT = (int64_t)1 << 22;
+#ifndef GSR_SORT_SMALL_LIMIT_LOG2
+#define GSR_SORT_SMALL_LIMIT_LOG2 21
+#endif
+constexpr int64_t SORT_SMALL_TILE_LIMIT = (int64_t)1 << GSR_SORT_SMALL_LIMIT_LOG2;
 constexpr int64_t SORT_SMALL_LIMIT = (int64_t)1 << 30;  // below: 32-bit look-back words, above: 64-bit
 constexpr int SORT_MAX_PASSES = 8;
 constexpr int SORT_LB_GROUP = 8;   // tiles per look-back group (radix_sort.cu)
