@@ -4,17 +4,17 @@
 // ascending, stable, on key bits [0, end_bit).  No CUB / Thrust.
 //
 //   1. digit histograms of every pass: built by the producer of the keys where that is cheaper
-//      (duplicate_tiles_kernel), else by sort_histogram_kernel (one read of the keys, warp-aggregated
-//      shared-memory atomics so that a digit with two or three populated bins does not serialise);
+//      (duplicate_tiles_kernel), else by sort_histogram_kernel (one read of the keys, few long-running blocks);
 //   2. one scatter kernel per digit (SortPlan: ceil(end_bit / 8) digits of nearly equal width, e.g. 7 + 6
 //      bits for the 13-bit tile ids of a 1080p image: fewer bins mean longer coalesced runs per digit in
-//      the scatter).  Each block takes a tile of 256 x ITEMS pairs (dynamic ticket), ranks its keys with
-//      warp-level __match_any_sync multi-split into per-warp shared-memory digit counters (stable: item
-//      order inside a warp is preserved), chains tile prefixes with a decoupled look-back over per-digit
-//      status words, stages the tile in shared memory in sorted order and writes it out in per-digit runs.
+//      the scatter).  Each block takes a tile of 256 x ITEMS pairs (dynamic ticket), ranks its keys per warp
+//      through a shared-memory peer table (stable: item order inside a warp is preserved), stages the keys in
+//      sorted order, requests the values, chains tile prefixes with a two-level decoupled look-back over
+//      per-digit status words and writes the tile out in per-digit runs.  Every block redoes the exclusive
+//      scan of the 256-bin histogram itself (no kernel launch between the passes).
 // The pair count may live on the device (n_dev): the grid is then sized from a capacity and surplus blocks
 // leave at once -- the forward pass sorts the (tile, Gaussian) list without the host knowing its length.
-// HBM traffic: 8 B/pair for a separate histogram + 16 B/pair/pass (u32 keys), 24 B/pair/pass (u64 keys).
+// HBM traffic: 4 B/pair for a separate histogram of u32 keys + 16 B/pair/pass (u32 keys), 24 B/pair/pass (u64).
 #include <cstdlib>
 #include "common.cuh"
 
@@ -33,8 +33,8 @@ template <> struct St<unsigned long long> {
 constexpr int NWARPS = SORT_THREADS / 32;
 
 // make EXTRA=-DGSR_SORT_PROFILE: cycles per phase of sort_tile summed over tiles (thread 0 of each block), read
-// with gsr_debug_sort_profile: [0] tiles, [1] load, [2] rank, [3] count + publish + scan, [4] look-back, [5] stage,
-// [6] write-out
+// with gsr_debug_sort_profile: [0] tiles, [1] load, [2] rank, [5] count + scan + stage keys + request values,
+// [7] in-group part of the look-back (thread 0's digit), [4] rest of the look-back + stage values, [6] write-out
 __device__ unsigned long long g_sort_prof[8];
 #ifdef GSR_SORT_PROFILE
 #define SORT_TICK(i) do { if (threadIdx.x == 0) { const long long _t = clock64(); atomicAdd(&g_sort_prof[i], (unsigned long long)(_t - _t0)); _t0 = _t; } } while (0)

@@ -181,6 +181,38 @@ def test_radix_sort_is_stable_and_matches_numpy(n, end_bit):
     assert np.array_equal(vo, vals[order])
 
 
+@pytest.mark.parametrize("n_cap,n,end_bit", [(1, 1, 32), (5000, 4097, 13), (300_000, 300_000, 32), (300_000, 123_457, 17),
+                                             (6_000_000, 5_100_000, 13), (70_000, 0, 9)])
+def test_radix_sort_u32_with_a_device_side_count(n_cap, n, end_bit):
+    """The form the forward pass uses (gsr_sort_pairs_u32): u32 keys, digit widths from the plan (7 + 6 bits for 13),
+    2048- or 4096-pair tiles, and the pair count read on the device (n <= capacity; the grid is sized from the capacity).
+    Stable, only bits [0, end_bit) compared, nothing written past n."""
+    from diff_gaussian_rasterization import _abi
+    lib = _abi.lib()
+    rng = np.random.default_rng(n_cap + n + end_bit)
+    keys = rng.integers(0, 1 << 32, n_cap, dtype=np.uint64).astype(np.uint32)
+    if n > 1000:
+        keys[: n // 2] = keys[rng.integers(0, 37, n // 2)]  # many duplicates -> exercises stability
+    vals = rng.permutation(n_cap).astype(np.uint32)
+    k_in, v_in = torch.from_numpy(keys.view(np.int32)).cuda(), torch.from_numpy(vals.view(np.int32)).cuda()
+    k_out, v_out = torch.full_like(k_in, -1), torch.full_like(v_in, -1)
+    n_dev = torch.tensor([n], dtype=torch.int32, device="cuda")
+    tb = lib.gsr_sort_u32_temp_bytes(n_cap)
+    temp = torch.empty(max(tb, 1), dtype=torch.uint8, device="cuda")
+    p = lambda t: C.c_void_p(t.data_ptr())
+    r = lib.gsr_sort_pairs_u32(p(k_in), p(k_out), p(v_in), p(v_out), n_cap, p(n_dev), end_bit, p(temp), tb, None)
+    assert r == 0, _abi.last_error()
+    torch.cuda.synchronize()
+    ko, vo = k_out.cpu().numpy().view(np.uint32), v_out.cpu().numpy().view(np.uint32)
+    mask = np.uint32((1 << end_bit) - 1) if end_bit < 32 else np.uint32(0xFFFFFFFF)
+    order = np.argsort(keys[:n] & mask, kind="stable")
+    assert np.array_equal(ko[:n], keys[:n][order])
+    assert np.array_equal(vo[:n], vals[:n][order])
+    passes = (end_bit + 7) // 8
+    if passes % 2 == 1 and n < n_cap:  # odd pass count: the output buffers are only ever written by the last pass
+        assert (ko[n:] == 0xFFFFFFFF).all() and (vo[n:] == 0xFFFFFFFF).all()
+
+
 def test_radix_sort_ignores_bits_above_end_bit():
     """cub::DeviceRadixSort semantics (rasterizer_impl.cu:303-308): only bits [0, end_bit) are compared."""
     rng = np.random.default_rng(3)
