@@ -69,7 +69,7 @@ __device__ __forceinline__ void red_add4(float4* p, float4 v) {
 //              dL_dmean2D may be NULL.
 // SPLIT / RAW: the N3 extensions (gsr_inputs::shs_rest, ::raw_params) are compiled out of the standard kernels
 template <bool ACC, bool SPLIT, bool RAW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)  // 128 registers: two resident blocks (some variants took 134-194 and ran one per SM)
 preprocess_bwd_kernel(gsr_inputs in, Geom g, const int32_t* __restrict__ radii, const float* __restrict__ accum,
                       float* __restrict__ dL_dmean2D, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor,
                       float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
