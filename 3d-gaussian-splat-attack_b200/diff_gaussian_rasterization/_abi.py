@@ -67,6 +67,8 @@ EXPORTS = {
     "gsr_sort_u32_temp_bytes": (C.c_size_t, [C.c_int64]),
     "gsr_sort_pairs_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),
+    "gsr_sort_pairs_u32_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
+                                            C.c_void_p]),
     "gsr_profile_enable": (C.c_int, [C.c_int]),
     "gsr_profile_read": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gsr_launch_count": (C.c_int64, [C.c_int]),

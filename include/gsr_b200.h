@@ -194,6 +194,19 @@ int gsr_sort_pairs_u32(const uint32_t* keys_in, uint32_t* keys_out, const uint32
                        int64_t n_cap, const uint32_t* n_dev, int32_t end_bit, void* temp, size_t temp_bytes,
                        void* stream);
 
+/* The same (u32 key, u32 value) sort for callers that cannot allocate device memory or hand over a temp buffer (code
+ * under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The temp block lives in a file-scope __device__ array inside the library
+ * (csrc/static_scratch.cu): GSR_STATIC_SORT_SCRATCH_BYTES on every GPU that loads the library, held until the process
+ * exits.  n > GSR_STATIC_SORT_MAX_PAIRS returns GSR_ERR_CAPACITY.  Calls nothing that allocates.  All calls on a
+ * device share the array (each call clears the part it needs on `stream` first): calls that overlap on the GPU --
+ * different streams without an ordering between them -- race; order them or use gsr_sort_pairs_u32.  keys_in ==
+ * keys_out (and vals) is allowed when ceil(end_bit / 8) is even.  Same result as gsr_sort_pairs_u32, bit for bit. */
+#define GSR_STATIC_SORT_MAX_PAIRS (1 << 20)
+#define GSR_STATIC_SORT_SCRATCH_BYTES (21 * 512 * 1024) /* 10.5 MiB >= gsr_sort_u32_temp_bytes(GSR_STATIC_SORT_MAX_PAIRS) */
+int gsr_sort_pairs_u32_static(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                              int64_t n, int32_t end_bit, void* stream);
+
 /* Copies internal arrays of a finished forward out for inspection. name is one of: "depths",
  * "means2D", "cov3D", "conic_opacity", "rgb", "clamped", "tiles_touched", "point_offsets", "rects",
  * "perm", "offsets_sorted", "final_T", "n_contrib", "ranges", "tiles_sorted", "keys_sorted".
