@@ -328,6 +328,73 @@ int gsr_backward_accumulate_phase(const gsr_inputs* in, const void* geom, const 
                        dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, true, phase, stream);
 }
 
+size_t gsr_view_accum_bytes(int32_t P) { return align_up((size_t)(P > 0 ? P : 0) * 12 * sizeof(float)); }
+
+int gsr_backward_blend_view(const gsr_inputs* in, const void* geom, int64_t L, const uint32_t* point_list,
+                            const void* image, const float* dL_dpix, float* accum, void* stream) {
+  GSR_TRY(check_inputs(in));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (in->P == 0) return GSR_OK;
+  if (!geom || !image || !dL_dpix || !accum || (L > 0 && !point_list)) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  if (in->K > 0) { set_error("backward_blend_view: object channels are not supported"); return GSR_ERR_INVALID; }
+  if (misaligned16(accum)) { set_error("accum must be 16-byte aligned"); return GSR_ERR_INVALID; }
+  Geom g(const_cast<void*>(geom), in->P);
+  Image im(const_cast<void*>(image), in->W, in->H);
+  {
+    StageScope ps(ST_BLEND_BWD, st);
+    GSR_TRY(launch_blend_bwd(*in, g, im, point_list, dL_dpix, nullptr, accum, nullptr, st));
+  }
+  return debug_sync(in, st, "blend_bwd");
+}
+
+int gsr_backward_preprocess_views(const gsr_inputs* in, int32_t n_views, const gsr_view_ref* views,
+                                  int32_t accumulate, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
+                                  float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* stream) {
+  if (!in) { set_error("inputs is NULL"); return GSR_ERR_INVALID; }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (in->P < 0) { set_error("bad size P=%d", in->P); return GSR_ERR_INVALID; }
+  if (in->P == 0 || n_views == 0) return GSR_OK;
+  if (n_views < 0 || n_views > GSR_MAX_FUSED_VIEWS || !views) {
+    set_error("backward_preprocess_views: 1..%d views per call, got %d", GSR_MAX_FUSED_VIEWS, n_views); return GSR_ERR_INVALID;
+  }
+  if (in->raw_params || in->shs_rest || in->K > 0) {
+    set_error("backward_preprocess_views: raw_params / shs_rest / object channels are not supported"); return GSR_ERR_INVALID;
+  }
+  if (!in->means3D || (in->shs == nullptr) == (in->colors_precomp == nullptr)) {
+    set_error("Please provide excatly one of either SHs or precomputed colors!"); return GSR_ERR_INVALID;
+  }
+  const bool sr = in->scales != nullptr && in->rotations != nullptr;
+  if (sr == (in->cov3D_precomp != nullptr) || ((in->scales != nullptr) != (in->rotations != nullptr))) {
+    set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    return GSR_ERR_INVALID;
+  }
+  if (in->shs && (in->M < 1 || in->M > 16 || in->D < 0 || in->D > 3 || (in->D + 1) * (in->D + 1) > in->M)) {
+    set_error("SH degree %d / M=%d not supported by the multi-view backward (M <= 16)", in->D, in->M); return GSR_ERR_INVALID;
+  }
+  if (!dL_dopacity || !dL_dmean3D || (in->shs && !dL_dsh) || (in->scales && (!dL_dscale || !dL_drot)) ||
+      (in->cov3D_precomp && !dL_dcov3D) || (in->colors_precomp && !dL_dcolor)) {
+    set_error("a gradient buffer is NULL for an input that was given"); return GSR_ERR_INVALID;
+  }
+  if (misaligned16(in->shs) || misaligned16(in->rotations) || misaligned16(dL_dsh) || misaligned16(dL_drot)) {
+    set_error("shs, rotations, dL_dsh and dL_drot must be 16-byte aligned"); return GSR_ERR_INVALID;
+  }
+  for (int v = 0; v < n_views; v++) {
+    const gsr_view_ref& r = views[v];
+    if (!r.viewmatrix || !r.projmatrix || !r.campos || !r.geom || !r.radii || !r.accum || r.W <= 0 || r.H <= 0) {
+      set_error("backward_preprocess_views: view %d has a NULL pointer or a bad size", v); return GSR_ERR_INVALID;
+    }
+    if (misaligned16(r.accum) || misaligned16(r.geom)) { set_error("view %d: accum / geom must be 16-byte aligned", v); return GSR_ERR_INVALID; }
+  }
+  {
+    StageScope ps(ST_PREPROCESS_BWD, st);
+    GSR_TRY(launch_preprocess_bwd_views(*in, n_views, views, accumulate != 0, dL_dopacity,
+                                        in->colors_precomp ? dL_dcolor : nullptr, dL_dmean3D,
+                                        in->cov3D_precomp ? dL_dcov3D : nullptr, in->shs ? dL_dsh : nullptr,
+                                        in->scales ? dL_dscale : nullptr, in->scales ? dL_drot : nullptr, st));
+  }
+  return debug_sync(in, st, "preprocess_bwd_views");
+}
+
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* /*projmatrix*/,
                      uint8_t* present, void* stream) {
   if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) { set_error("mark_visible: bad arguments"); return GSR_ERR_INVALID; }

@@ -280,6 +280,9 @@ int launch_preprocess_bwd(const gsr_inputs& in, const Geom& g, const int32_t* ra
                           float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
                           float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, bool accumulate,
                           cudaStream_t st);
+int launch_preprocess_bwd_views(const gsr_inputs& in, int n_views, const gsr_view_ref* views, bool accumulate,
+                                float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
+                                float* dL_dsh, float* dL_dscale, float* dL_drot, cudaStream_t st);
 int launch_pgd_linf(float* p, const float* g, const float* p0, int64_t n, float alpha, float eps, cudaStream_t st);
 int launch_pgd_l2(float* p, const float* g, const float* p0, int64_t rows, int width, float alpha, float eps,
                   double* sumsq_scratch, cudaStream_t st);

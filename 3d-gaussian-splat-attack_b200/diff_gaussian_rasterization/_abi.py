@@ -13,7 +13,8 @@ LIB_PATH = os.environ.get("GSR_B200_LIB") or os.path.join(_ROOT, "lib", "libgsr_
 CSRC_DIR = os.path.join(_ROOT, "csrc")
 
 GSR_OK, GSR_ERR_INVALID, GSR_ERR_CUDA, GSR_ERR_CAPACITY, GSR_ERR_PREFILTERED = 0, -1, -2, -3, -4
-ABI_VERSION = 3
+ABI_VERSION = 4
+MAX_FUSED_VIEWS = 8  # GSR_MAX_FUSED_VIEWS
 
 
 class GsrInputs(C.Structure):
@@ -26,6 +27,15 @@ class GsrInputs(C.Structure):
         ("opacities", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
         ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p), ("obj_feats", C.c_void_p),
         ("shs_rest", C.c_void_p), ("dL_dshs_rest", C.c_void_p),
+    ]
+
+
+class GsrViewRef(C.Structure):
+    """struct gsr_view_ref (include/gsr_b200.h): one forwarded view as the multi-view backward sees it."""
+    _fields_ = [
+        ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("W", C.c_int32), ("H", C.c_int32),
+        ("geom", C.c_void_p), ("radii", C.c_void_p), ("accum", C.c_void_p), ("dL_dmean2D", C.c_void_p),
     ]
 
 
@@ -61,6 +71,11 @@ EXPORTS = {
     "gsr_backward_accumulate_phase": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                                 C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p] + [C.c_void_p] * 8 +
                                       [C.c_int32, C.c_void_p]),
+    "gsr_view_accum_bytes": (C.c_size_t, [C.c_int32]),
+    "gsr_backward_blend_view": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p]),
+    "gsr_backward_preprocess_views": (C.c_int, [C.POINTER(GsrInputs), C.c_int32, C.POINTER(GsrViewRef), C.c_int32] +
+                                      [C.c_void_p] * 7 + [C.c_void_p]),
     "gsr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_sort_pairs_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),

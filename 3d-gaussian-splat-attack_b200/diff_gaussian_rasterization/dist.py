@@ -140,7 +140,6 @@ def sharded_accumulate_step(settings: Sequence, inputs: Dict[str, torch.Tensor],
     world = (dist.get_world_size(group) if on else 1) if world is None else world
     if set(bucket.params) != set(inputs):
         raise ValueError(f"bucket is keyed {sorted(bucket.params)}, inputs {sorted(inputs)}")
-    bucket.zero()
     grads = {n: bucket.grad(n) for n in inputs}
     plain = {n: t.detach() for n, t in inputs.items()}
     total = torch.zeros((), dtype=bucket.flat.dtype, device=bucket.flat.device)
@@ -160,13 +159,15 @@ def sharded_accumulate_step(settings: Sequence, inputs: Dict[str, torch.Tensor],
             loss = loss_fn(image, mine[i])
             losses.append(loss.detach())
             return torch.autograd.grad(loss, image)[0]
-        vp.step([settings[k] for k in mine], dL_fn, grads, plain["means3D"], plain["opacities"], **extra)
+        # overwrite: the step SETS the bucket slices to the sum over this rank's cameras (no zeroing pass)
+        vp.step([settings[k] for k in mine], dL_fn, grads, plain["means3D"], plain["opacities"], overwrite=True, **extra)
         for l in losses:
             total = total + l.to(total.dtype)
     else:
         if forward_view is None or backward_view is None:
             from . import views as _v
             forward_view, backward_view = forward_view or _v.forward_view, backward_view or _v.backward_view
+        bucket.zero()
         for k in mine:
             image, _radii, state = forward_view(settings[k], plain["means3D"], plain["opacities"], **extra)
             image = image.detach().requires_grad_(True)

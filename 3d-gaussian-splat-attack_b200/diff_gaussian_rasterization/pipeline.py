@@ -153,8 +153,7 @@ class HostStepPipeline:
         cur.wait_event(slot.ev_in)
         if slot.used:
             cur.wait_event(slot.ev_out)  # the previous gradients of this slot have left
-        slot.grad.zero_()
-        p = slot.p
+        p = slot.p  # (no zeroing of slot.grad: the step below overwrites it; the padding between slices stays zero)
         settings = []
         for v in range(self.n_views):
             cm = slot.cam[v]
@@ -163,7 +162,7 @@ class HostStepPipeline:
                 scale_modifier=1.0, viewmatrix=cm[0:16].view(4, 4), projmatrix=cm[16:32].view(4, 4),
                 sh_degree=self.sh_degree, campos=cm[32:35], prefiltered=False, debug=False))
         self.views.step(settings, lambda img, k: slot.dL[k], slot.g, p["means3D"], p["opacities"], shs=p["shs"],
-                        scales=p["scales"], rotations=p["rotations"])
+                        scales=p["scales"], rotations=p["rotations"], overwrite=True)
         if self.world > 1:
             import torch.distributed as dist
             if self.share:  # rank r keeps slice r of the sum

@@ -19,7 +19,7 @@ import torch
 from . import _abi
 from . import _f32c, _make_inputs, _ptr, _run_forward, _state
 
-__all__ = ["ViewState", "forward_view", "backward_view", "ViewPipeline", "GRAD_KEYS"]
+__all__ = ["ViewState", "forward_view", "backward_view", "backward_views", "ViewPipeline", "GRAD_KEYS"]
 
 # gradient buffers backward_view() accepts, named after GaussianRasterizer.forward's arguments
 GRAD_KEYS = ("means3D", "means2D", "opacities", "shs", "shs_rest", "colors_precomp", "scales", "rotations", "cov3D_precomp")
@@ -147,10 +147,113 @@ def backward_view(state: ViewState, dL_dimage: torch.Tensor, grads: Dict[str, Op
             stream.synchronize()
 
 
+def _view_ref(inp, geom, radii, accum, mean2D=None):
+    """gsr_view_ref of one forwarded view (camera fields from the gsr_inputs its forward used)."""
+    r = _abi.GsrViewRef()
+    r.viewmatrix, r.projmatrix, r.campos = inp.viewmatrix, inp.projmatrix, inp.campos
+    r.tanfovx, r.tanfovy, r.W, r.H = inp.tanfovx, inp.tanfovy, inp.W, inp.H
+    r.geom, r.radii, r.accum, r.dL_dmean2D = _ptr(geom), _ptr(radii), _ptr(accum), _ptr(mean2D)
+    return r
+
+
+def _preprocess_views(lib, inp, refs, accumulate, grads, stream):
+    """One gsr_backward_preprocess_views call over up to MAX_FUSED_VIEWS gsr_view_ref's."""
+    arr = (_abi.GsrViewRef * len(refs))(*refs)
+    g = lambda n: _ptr(grads.get(n))
+    _abi.check(lib.gsr_backward_preprocess_views(
+        C.byref(inp), len(refs), arr, int(bool(accumulate)), g("opacities"), g("colors_precomp"), g("means3D"),
+        g("cov3D_precomp"), g("shs"), g("scales"), g("rotations"), C.c_void_p(stream.cuda_stream)),
+        "backward_preprocess_views")
+
+
+def backward_views(states, dL_dimages, grads: Dict[str, Optional[torch.Tensor]], accumulate: bool = True,
+                   means2D_grads=None) -> None:
+    """Backward of SEVERAL forwarded views of the same Gaussians with the per-Gaussian half done once for all of
+    them (gsr_backward_blend_view per view, then gsr_backward_preprocess_views per group of up to 8 views): every
+    Gaussian's attributes are read once and its gradient rows written once per group instead of once per view.
+    `states` / `dL_dimages`: ViewStates of forward_view calls on the SAME input tensors and dL/dimage of each.
+    accumulate=True ADDS the summed gradients to `grads` (as repeated backward_view calls would, up to summation
+    order); accumulate=False overwrites `grads` (rows of Gaussians no view rendered become zero), so the caller
+    need not zero them.  `means2D_grads`: optional list of per-view (P,3) tensors for the screen-space gradients
+    (they are per view, not summed).  Fused activations (raw_params / shs_rest) are not supported here."""
+    if len(states) != len(dL_dimages):
+        raise Exception("one dL_dimage per view state")
+    if not states:
+        return
+    s0 = states[0]
+    P, t = s0.P, s0.tensors
+    if P == 0:
+        return
+    for st_ in states:
+        if st_.P != P or st_.M != s0.M or st_.raw_params or st_.tensors.get("shs_rest") is not None or \
+                any(st_.tensors[k] is not t[k] and (st_.tensors[k] is None or t[k] is None or
+                                                   st_.tensors[k].data_ptr() != t[k].data_ptr())
+                    for k in ("means3D", "shs", "colors_precomp", "opacities", "scales", "rotations", "cov3D_precomp")):
+            raise Exception("backward_views: all views must come from forward_view on the same input tensors, "
+                            "without raw_params / shs_rest")
+    for k in grads:
+        if k not in GRAD_KEYS:
+            raise Exception(f"unknown gradient buffer '{k}' (expected one of {GRAD_KEYS})")
+    for name, key in (("means3D", "means3D"), ("opacities", "opacities"), ("shs", "shs"), ("colors_precomp", "colors_precomp"),
+                      ("scales", "scales"), ("rotations", "rotations"), ("cov3D_precomp", "cov3D_precomp")):
+        if t[key] is None:
+            continue
+        gbuf = grads.get(name)
+        if gbuf is None:
+            raise Exception(f"grads['{name}'] is required for the inputs these views were rendered with")
+        if not gbuf.is_cuda or gbuf.dtype != torch.float32 or not gbuf.is_contiguous() or gbuf.numel() != t[key].numel():
+            raise RuntimeError(f"grads['{name}'] must be a contiguous float32 CUDA tensor shaped like the input")
+        _check_aligned(name, gbuf)
+    m2_sum = grads.get("means2D")  # summed over the views, as repeated backward_view calls leave it
+    if m2_sum is not None:
+        if means2D_grads is not None:
+            raise Exception("pass either grads['means2D'] (summed over the views) or means2D_grads (one per view)")
+        if not m2_sum.is_cuda or m2_sum.dtype != torch.float32 or not m2_sum.is_contiguous() or m2_sum.numel() != 3 * P:
+            raise RuntimeError("grads['means2D'] must be a contiguous float32 CUDA tensor with 3*P elements")
+        if not accumulate:
+            m2_sum.zero_()
+    dev = t["means3D"].device
+    with torch.no_grad(), torch.cuda.device(dev):
+        lib = _abi.lib()
+        stream = torch.cuda.current_stream(dev)
+        sp = C.c_void_p(stream.cuda_stream)
+        F = _abi.MAX_FUSED_VIEWS
+        first = m2_sum is None  # with a summed means2D buffer every group runs in adding mode
+        if not accumulate and not first:
+            for k, gbuf in grads.items():
+                if gbuf is not None:
+                    gbuf.zero_()
+        for c0 in range(0, len(states), F):
+            refs, keep = [], []
+            for i in range(c0, min(c0 + F, len(states))):
+                st_ = states[i]
+                rs = st_.rs
+                H, W = int(rs.image_height), int(rs.image_width)
+                dpix = _f32c(dL_dimages[i], "dL_dimage")
+                if dpix is None or dpix.numel() != 3 * H * W:
+                    raise RuntimeError(f"dL_dimage must have 3*{H}*{W} elements")
+                inp = _make_inputs(rs, P, st_.M, 0, t["means3D"], t["shs"], t["colors_precomp"], t["opacities"],
+                                   t["scales"], t["rotations"], t["cov3D_precomp"], None, keep)
+                accum = torch.empty(lib.gsr_view_accum_bytes(P) // 4, dtype=torch.float32, device=dev)
+                _abi.check(lib.gsr_backward_blend_view(C.byref(inp), _ptr(st_.geom), st_.L, _ptr(st_.point_list),
+                                                       _ptr(st_.image), _ptr(dpix), _ptr(accum), sp), "backward_blend_view")
+                m2 = means2D_grads[i] if means2D_grads is not None else None
+                if m2 is not None and (not m2.is_cuda or m2.dtype != torch.float32 or not m2.is_contiguous() or m2.numel() != 3 * P):
+                    raise RuntimeError("means2D_grads[i] must be a contiguous float32 CUDA tensor with 3*P elements")
+                if m2 is not None and not accumulate and not first:
+                    m2.zero_()  # later groups run in adding mode (for the summed buffers); per-view buffers start at 0
+                refs.append(_view_ref(inp, st_.geom, st_.radii, accum, m2 if m2_sum is None else m2_sum))
+                keep.extend([accum, dpix, inp])
+            _preprocess_views(lib, keep[-1], refs, accumulate or not first, grads, stream)
+            first = False
+        if s0.rs.debug:
+            stream.synchronize()
+
+
 class _PipeSlot:
     def __init__(self, dev):
         self.dev = dev
-        self.geom = self.image = self.radii = None
+        self.geom = self.image = self.radii = self.accum = None
         self.point_list = torch.empty(0, dtype=torch.int32, device=dev)
         self.count_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         self.count_host = torch.zeros(1, dtype=torch.int32).pin_memory()
@@ -175,9 +278,18 @@ class ViewPipeline:
     backward's accumulators.  Results are those of forward_view / backward_view (same kernels, same order of
     accumulation into `grads`)."""
 
-    def __init__(self, device=None, n_slots: int = 3, overlap: bool = True):
+    def __init__(self, device=None, n_slots: int = 3, overlap: bool = True, fuse_backward: int = _abi.MAX_FUSED_VIEWS):
+        """fuse_backward = F > 1: the per-Gaussian half of the backward (preprocess_bwd) is deferred and done ONCE per
+        group of up to F cameras (gsr_backward_preprocess_views: attributes read once, gradient rows written once per
+        group instead of once per camera); each slot then keeps its own 48-byte-per-Gaussian accumulator and the ring
+        grows to F + 2 slots.  fuse_backward <= 1: one preprocess_bwd per camera, as backward_view does."""
         if n_slots < 2:
             raise ValueError("n_slots must be >= 2")
+        self.fuse = max(1, min(int(fuse_backward), _abi.MAX_FUSED_VIEWS))
+        if self.fuse > 1:
+            n_slots = max(n_slots, self.fuse + 2)
+        self.pending = []     # slots whose blend_bwd has been queued and whose per-Gaussian backward is deferred
+        self.overwrite_next = False  # the next deferred pass SETS the gradient rows instead of adding to them
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.dev = dev
         self.overlap = overlap
@@ -212,6 +324,7 @@ class ViewPipeline:
             slot.geom = self._ensure(None, lib.gsr_geom_bytes(P))
             slot.image = self._ensure(None, lib.gsr_image_bytes(W, H))
             slot.radii = torch.empty((P,), dtype=torch.int32, device=self.dev)
+            slot.accum = None
             slot.sig = sig
         self.scratch = self._ensure(self.scratch, lib.gsr_scratch_bytes(P, max(slot.point_list.numel(), 1), W, H))
         keep = []
@@ -249,7 +362,7 @@ class ViewPipeline:
                                          _ptr(color), None, C.c_void_p(R.cuda_stream)), "forward_blend")
         return color
 
-    def _backward(self, slot, rs, t, P, M, dL_dimage, grads):
+    def _backward(self, slot, rs, t, P, M, dL_dimage, grads, fused=False):
         lib = _abi.lib()
         R = torch.cuda.current_stream(self.dev)
         H, W = int(rs.image_height), int(rs.image_width)
@@ -265,6 +378,17 @@ class ViewPipeline:
                 g("means3D"), g("cov3D_precomp"), g("shs"), g("scales"), g("rotations"), ph,
                 C.c_void_p(stream.cuda_stream)), "backward_accumulate")
 
+        if fused:
+            # per-tile half now, into the slot's own accumulator; the per-Gaussian half of the whole group later
+            if slot.accum is None:
+                slot.accum = torch.empty(lib.gsr_view_accum_bytes(P) // 4, dtype=torch.float32, device=self.dev)
+            _abi.check(lib.gsr_backward_blend_view(C.byref(slot.inp), _ptr(slot.geom), slot.L, _ptr(slot.point_list),
+                                                   _ptr(slot.image), _ptr(dpix), _ptr(slot.accum),
+                                                   C.c_void_p(R.cuda_stream)), "backward_blend_view")
+            self.pending.append(slot)
+            if len(self.pending) >= self.fuse:
+                self._flush_pending(grads)
+            return
         if not self.overlap:
             phase(3, R)
             slot.ev_done.record(R)
@@ -282,15 +406,41 @@ class ViewPipeline:
             self.pb_pending = True
         slot.busy = True
 
+    def _flush_pending(self, grads):
+        """The deferred per-Gaussian backward of the cameras in self.pending, once for all of them, on stream B (under
+        the next camera's blending) -- or on the caller's stream without overlap."""
+        if not self.pending:
+            return
+        lib = _abi.lib()
+        R = torch.cuda.current_stream(self.dev)
+        refs = [_view_ref(sl.inp, sl.geom, sl.radii, sl.accum, grads.get("means2D")) for sl in self.pending]
+        if self.overlap:
+            self.ev_bb.record(R)
+            self.B.wait_event(self.ev_bb)
+            stream = self.B
+        else:
+            stream = R
+        _preprocess_views(lib, self.pending[0].inp, refs, not self.overwrite_next, grads, stream)
+        self.overwrite_next = False
+        for sl in self.pending:
+            sl.ev_done.record(stream)
+            sl.busy = True
+        if self.overlap:
+            self.ev_pb.record(self.B)
+            self.pb_pending = True
+        self.pending = []
+
     # ---- public -------------------------------------------------------------------------------------------
     def step(self, settings, dL_fn, grads, means3D, opacities, shs=None, colors_precomp=None, scales=None,
-             rotations=None, cov3D_precomp=None, shs_rest=None, raw_params=False):
+             rotations=None, cov3D_precomp=None, shs_rest=None, raw_params=False, overwrite=False):
         """Render every camera in `settings` (GaussianRasterizationSettings) and ADD its gradients to `grads` (as
         backward_view does).  `dL_fn(image, k)` receives the plain (3,H,W) render of camera k on the current stream
         and returns dL/dimage -- or None to skip that camera's backward (forward-only use).  Returns the list of
         duplicate counts (num_rendered) per camera.  `shs_rest` / `raw_params` as in forward_view (fused model
         activations; gradients then refer to the raw parameters, `grads["shs"]` to the DC block and
-        `grads["shs_rest"]` to the rest block)."""
+        `grads["shs_rest"]` to the rest block).  overwrite=True SETS `grads` to the sum over this step's cameras
+        instead of adding to it: the caller need not zero the buffers, and with the deferred per-Gaussian backward
+        (fuse_backward > 1) the first group's pass writes each row without reading it."""
         if (shs is None) == (colors_precomp is None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
         if ((scales is None or rotations is None) and cov3D_precomp is None) or \
@@ -306,6 +456,10 @@ class ViewPipeline:
         P, n = means3D.size(0), len(settings)
         counts = []
         if P == 0 or n == 0:
+            if overwrite:
+                for gbuf in grads.values():
+                    if gbuf is not None:
+                        gbuf.zero_()
             return counts
         with torch.no_grad(), torch.cuda.device(self.dev):
             t = dict(means3D=_f32c(means3D, "means3D"), shs=_f32c(shs, "shs"),
@@ -335,6 +489,13 @@ class ViewPipeline:
             if self.overlap:  # whatever produced the inputs on the caller's stream must be visible to G
                 self.ev_start.record(R)
                 self.G.wait_event(self.ev_start)
+            fused = self.fuse > 1 and not raw_params and t["shs_rest"] is None and (M <= 16)
+            self.overwrite_next = bool(overwrite) and fused and grads.get("means2D") is None and \
+                any(g is not None for g in grads.values())
+            if overwrite and not self.overwrite_next:
+                for gbuf in grads.values():
+                    if gbuf is not None:
+                        gbuf.zero_()
             ns = len(self.slots)
             self._geometry(self.slots[0], settings[0], t, P, M, grads, raw_params)
             self._binning(self.slots[0], settings[0], P)
@@ -347,12 +508,18 @@ class ViewPipeline:
                 with torch.enable_grad():
                     dL = dL_fn(color, k)
                 if dL is not None:
-                    self._backward(slot, settings[k], t, P, M, dL, grads)
+                    self._backward(slot, settings[k], t, P, M, dL, grads, fused)
                 else:
                     slot.ev_done.record(R)
                     slot.busy = True
                 if k + 1 < n:
                     self._binning(self.slots[(k + 1) % ns], settings[k + 1], P)
+            self._flush_pending(grads)
+            if self.overwrite_next:  # no camera had a backward: the sum over no cameras is zero
+                for gbuf in grads.values():
+                    if gbuf is not None:
+                        gbuf.zero_()
+                self.overwrite_next = False
             if self.overlap:  # later work on the caller's stream (and frees of the inputs) must follow G's and B's
                 ev = torch.cuda.Event()
                 ev.record(self.G)

@@ -299,8 +299,9 @@ class Workload:
         self.last_fn, self.last_radii, self.last_color = color.grad_fn, radii, color
 
     def step(self, dist=None, overlap=None):
-        self.flat_grad.zero_()
         overlap = self.overlap if overlap is None else overlap
+        if not (self.api == "views" and overlap):
+            self.flat_grad.zero_()  # (the pipelined step below overwrites the gradient slices itself)
         if self.api == "views" and overlap:
             from diff_gaussian_rasterization import views
             if self.vp is None:
@@ -308,7 +309,7 @@ class Workload:
                 self.settings_list = [self.settings(v) for v in range(len(self.cams))]
             p = self.params
             self.vp.step(self.settings_list, lambda img, k: self.dev_dL[k], self.grads, p["means3D"], p["opacities"],
-                         shs=p["shs"], scales=p["scales"], rotations=p["rotations"])
+                         shs=p["shs"], scales=p["scales"], rotations=p["rotations"], overwrite=True)
         else:
             for v in range(len(self.cams)):
                 self.view_fwd_bwd(v)

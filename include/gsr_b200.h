@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 3
+#define GSR_ABI_VERSION 4
 
 typedef enum {
   GSR_OK = 0,
@@ -156,6 +156,37 @@ int gsr_backward_accumulate_phase(const gsr_inputs* in, const void* geom, const 
                                   const float* dL_dpix, float* dL_dmean2D, float* dL_dopacity, float* dL_dcolor,
                                   float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                                   int32_t phase, void* stream);
+
+/* ---- backward of SEVERAL views with the per-Gaussian half done once for all of them (new; no counterpart in the
+ *      reference, whose backward.cu:144-396 kernels run once per camera and whose caller sums cameras through
+ *      autograd, attack.py:481-494).  Step 1, per view: gsr_backward_blend_view = the per-tile blending gradients
+ *      (renderCUDA backward, backward.cu:399-557) into that view's own accumulator `accum`
+ *      (gsr_view_accum_bytes(P) bytes, 256-byte aligned, zeroed by the call).  Step 2, once per group of up to
+ *      GSR_MAX_FUSED_VIEWS views: gsr_backward_preprocess_views reads each Gaussian's attributes once, loops over the
+ *      views that rendered it and writes (accumulate = 0: every row, zeros for Gaussians no view rendered) or adds
+ *      (accumulate = 1: rows of Gaussians at least one view rendered) the gradients summed over the views.
+ *      `in` supplies the scene (P, D, M, scale_modifier, means3D, shs, colors_precomp, scales, rotations,
+ *      cov3D_precomp); its camera fields are ignored, each view brings its own.  `views` is a HOST array.
+ *      The fused-activation inputs (raw_params, shs_rest) and K > 0 are not supported here (GSR_ERR_INVALID).
+ *      Results equal the sum of gsr_backward_accumulate over the views up to summation order. ---- */
+#define GSR_MAX_FUSED_VIEWS 8
+typedef struct gsr_view_ref {
+  const float* viewmatrix;  /* the view's camera, as in gsr_inputs                                        */
+  const float* projmatrix;
+  const float* campos;
+  float tanfovx, tanfovy;
+  int32_t W, H;
+  const void* geom;         /* that view's geometry state (gsr_forward_geometry)                           */
+  const int32_t* radii;     /* that view's radii (P)                                                       */
+  float* accum;             /* that view's accumulator: written by gsr_backward_blend_view                 */
+  float* dL_dmean2D;        /* optional per-view (P,3) screen-space gradient (written / added), or NULL    */
+} gsr_view_ref;
+size_t gsr_view_accum_bytes(int32_t P);
+int gsr_backward_blend_view(const gsr_inputs* in, const void* geom, int64_t L, const uint32_t* point_list,
+                            const void* image, const float* dL_dpix, float* accum, void* stream);
+int gsr_backward_preprocess_views(const gsr_inputs* in, int32_t n_views, const gsr_view_ref* views_host,
+                                  int32_t accumulate, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
+                                  float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* stream);
 
 /* ---- markVisible (rasterizer_impl.cu:141-153, checkFrustum :54-66); present is (P) bytes ---- */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
