@@ -47,6 +47,26 @@ struct ViewShared {
   float V[16], Pm[16], cam[3];
 };
 
+// The view loop is rolled and each iteration's loads depend on nothing but the Gaussian index, so what the next
+// iteration (and the SH phase) will read is requested into L2 ahead of time: no registers held, and the demand
+// load then pays an L2 hit instead of a DRAM round trip.
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_view_rows(const ViewShared& S, size_t idx) {
+  const char* ap = reinterpret_cast<const char*>(S.accum) + idx * 48;
+  prefetch_l2(ap);
+  prefetch_l2(ap + 32);  // a 48-byte row can straddle a 32-byte sector boundary pair / a 128-byte line
+  prefetch_l2(S.conic_opacity + idx);
+  prefetch_l2(S.clamped + idx);
+}
+
+struct ViewRows { float4 a0, a1, co; float a8; uint8_t cb; };
+__device__ __forceinline__ void load_view_rows(ViewRows& r, const ViewShared& S, size_t idx, bool sh) {
+  const float4* ap = reinterpret_cast<const float4*>(S.accum) + idx * 3;
+  r.a0 = ap[0]; r.a1 = ap[1]; r.a8 = ap[2].x;
+  r.co = S.conic_opacity[idx];
+  r.cb = sh ? S.clamped[idx] : (uint8_t)0;
+}
+
 template <bool ACC>
 __global__ void __launch_bounds__(FV_THREADS, 2)
 preprocess_bwd_views_kernel(gsr_inputs in, FusedViewsDev fv, float* __restrict__ dL_dopacity,
@@ -74,8 +94,27 @@ preprocess_bwd_views_kernel(gsr_inputs in, FusedViewsDev fv, float* __restrict__
   if (idx >= in.P) return;
   const int M = in.M;
 
+  // every load that depends on the Gaussian index only is issued here, before anything waits: the radii of all views
+  // (unrolled), the mean, and scale / rotation or the precomputed covariance
+  int32_t rad[FV_MAX];
+#pragma unroll
+  for (int v = 0; v < FV_MAX; v++) rad[v] = v < nv ? __ldg(sv[v].radii + idx) : 0;
+  const float mx = __ldg(in.means3D + 3 * (size_t)idx), my = __ldg(in.means3D + 3 * (size_t)idx + 1),
+              mz = __ldg(in.means3D + 3 * (size_t)idx + 2);
+  float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+  float s[3] = {0.f, 0.f, 0.f};   // scale_modifier * scale
+  float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f;  // 3D covariance (upper triangle)
+  if (in.scales) {
+    q = __ldg(reinterpret_cast<const float4*>(in.rotations) + idx);
+#pragma unroll
+    for (int k = 0; k < 3; k++) s[k] = in.scale_modifier * __ldg(in.scales + 3 * (size_t)idx + k);
+  } else {
+    const float* c3 = in.cov3D_precomp + 6 * (size_t)idx;
+    v0 = __ldg(c3); v1 = __ldg(c3 + 1); v2 = __ldg(c3 + 2); v3 = __ldg(c3 + 3); v4 = __ldg(c3 + 4); v5 = __ldg(c3 + 5);
+  }
   uint32_t live = 0;
-  for (int v = 0; v < nv; v++) live |= (uint32_t)(sv[v].radii[idx] > 0) << v;
+#pragma unroll
+  for (int v = 0; v < FV_MAX; v++) live |= (uint32_t)(rad[v] > 0) << v;
 
   if (!ACC) {  // per-view screen-space gradients of views that did not render this Gaussian: zero rows
     for (int v = 0; v < nv; v++) {
@@ -107,15 +146,22 @@ preprocess_bwd_views_kernel(gsr_inputs in, FusedViewsDev fv, float* __restrict__
     return;
   }
 
-  // ---- view-independent attributes, read once ----
-  const float mx = in.means3D[3 * (size_t)idx], my = in.means3D[3 * (size_t)idx + 1], mz = in.means3D[3 * (size_t)idx + 2];
-  float v0, v1, v2, v3, v4, v5;  // 3D covariance (upper triangle)
-  float R[3][3], s[3];            // R[c][k]: column c, row k ; s = scale_modifier * scale
+#ifndef GSR_VIEWS_NO_PREFETCH
+  if (in.shs) {  // the SH row is read after the view loop: request it now
+    const char* sp = reinterpret_cast<const char*>(in.shs) + (size_t)idx * M * 12;
+    prefetch_l2(sp);
+    if (M * 12 > 128) prefetch_l2(sp + 128);
+    if (M * 12 > 64) prefetch_l2(sp + M * 12 - 4);
+  }
+  {
+    const uint32_t later = live >> __ffs(live);
+    if (later) prefetch_view_rows(sv[__ffs(live) + __ffs(later) - 1], (size_t)idx);
+  }
+#endif
+  // ---- view-independent attributes (loaded above) ----
+  float R[3][3];  // R[c][k]: column c, row k
   if (in.scales) {
-    const float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
     const float r = q.x, x = q.y, y = q.z, z = q.w;
-#pragma unroll
-    for (int k = 0; k < 3; k++) s[k] = in.scale_modifier * in.scales[3 * (size_t)idx + k];
     R[0][0] = 1.f - 2.f * (y * y + z * z); R[0][1] = 2.f * (x * y - r * z); R[0][2] = 2.f * (x * z + r * y);
     R[1][0] = 2.f * (x * y + r * z); R[1][1] = 1.f - 2.f * (x * x + z * z); R[1][2] = 2.f * (y * z - r * x);
     R[2][0] = 2.f * (x * z - r * y); R[2][1] = 2.f * (y * z + r * x); R[2][2] = 1.f - 2.f * (x * x + y * y);
@@ -127,21 +173,30 @@ preprocess_bwd_views_kernel(gsr_inputs in, FusedViewsDev fv, float* __restrict__
     v3 = s0 * R[1][0] * R[1][0] + s1 * R[1][1] * R[1][1] + s2 * R[1][2] * R[1][2];
     v4 = s0 * R[1][0] * R[2][0] + s1 * R[1][1] * R[2][1] + s2 * R[1][2] * R[2][2];
     v5 = s0 * R[2][0] * R[2][0] + s1 * R[2][1] * R[2][1] + s2 * R[2][2] * R[2][2];
-  } else {
-    const float* c3 = in.cov3D_precomp + 6 * (size_t)idx;
-    v0 = c3[0]; v1 = c3[1]; v2 = c3[2]; v3 = c3[3]; v4 = c3[4]; v5 = c3[5];
   }
 
   // ---- phase A: screen-space gradients of every view -> 3D mean, 3D covariance, opacity, colour ----
   float dmean[3] = {0.f, 0.f, 0.f}, dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, dcol[3] = {0.f, 0.f, 0.f};
   float dop = 0.f;
-  for (int v = 0; v < nv; v++) {
-    if (!((live >> v) & 1)) continue;
+  // the rows of the NEXT live view are loaded (into registers) before the current view's arithmetic starts, and the
+  // rows of the one after that are requested into L2
+  ViewRows nxt;
+  int v = __ffs(live) - 1;
+  load_view_rows(nxt, sv[v], (size_t)idx, in.shs != nullptr);
+  while (v >= 0) {
     const ViewShared& S = sv[v];
-    const float4* ap = reinterpret_cast<const float4*>(S.accum) + (size_t)idx * 3;
-    const float4 a0 = ap[0], a1 = ap[1];
-    const float a8 = ap[2].x;
-    const float4 co = S.conic_opacity[idx];
+    const float4 a0 = nxt.a0, a1 = nxt.a1, co = nxt.co;
+    const float a8 = nxt.a8;
+    const uint8_t cb = nxt.cb;
+    const uint32_t later = live >> (v + 1);
+    const int vn = later ? v + __ffs(later) : -1;
+    if (vn >= 0) {
+      load_view_rows(nxt, sv[vn], (size_t)idx, in.shs != nullptr);
+#ifndef GSR_VIEWS_NO_PREFETCH
+      const uint32_t later2 = live >> (vn + 1);
+      if (later2) prefetch_view_rows(sv[vn + __ffs(later2)], (size_t)idx);
+#endif
+    }
     // a0 = dcolor.rgb, sum w dx ; a1 = sum w dy, sum w dx^2, sum w dx dy, sum w dy^2 ; a8 = sum w  (blend_bwd.cu)
     const float op = co.w;
     const float g2x = op * S.halfW * (-co.x * a0.w - co.y * a1.x);
@@ -209,13 +264,13 @@ preprocess_bwd_views_kernel(gsr_inputs in, FusedViewsDev fv, float* __restrict__
     dmean[2] += (Pm[8] * m_w - Pm[11] * mul1) * g2x + (Pm[9] * m_w - Pm[11] * mul2) * g2y;
     // ---- colour ----
     if (in.shs) {
-      const uint8_t cb = S.clamped[idx];
       s_rgb[v][0][tid] = (cb & 1) ? 0.f : a0.x;
       s_rgb[v][1][tid] = (cb & 2) ? 0.f : a0.y;
       s_rgb[v][2][tid] = (cb & 4) ? 0.f : a0.z;
     } else {
       dcol[0] += a0.x; dcol[1] += a0.y; dcol[2] += a0.z;
     }
+    v = vn;
   }
 
   // ---- geometry rows out: mean (without the SH direction term yet), opacity, colour, covariance / scale + rotation ----
@@ -229,7 +284,6 @@ preprocess_bwd_views_kernel(gsr_inputs in, FusedViewsDev fv, float* __restrict__
     if (dL_dcov3D) { for (int k = 0; k < 6; k++) dL_dcov3D[6 * (size_t)idx + k] = dcov[k]; }
   }
   if (in.scales) {  // 3D covariance -> scale / rotation (backward.cu:278-341), once for the sum over the views
-    const float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
     const float r = q.x, x = q.y, y = q.z, z = q.w;
     const float dS[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
                             {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
