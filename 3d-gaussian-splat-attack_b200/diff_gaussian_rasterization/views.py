@@ -422,6 +422,7 @@ class ViewPipeline:
             stream = R
         _preprocess_views(lib, self.pending[0].inp, refs, not self.overwrite_next, grads, stream)
         self.overwrite_next = False
+        self.last_group = list(self.pending)  # measurement hook (replay_last_group)
         for sl in self.pending:
             sl.ev_done.record(stream)
             sl.busy = True
@@ -429,6 +430,17 @@ class ViewPipeline:
             self.ev_pb.record(self.B)
             self.pb_pending = True
         self.pending = []
+
+    def replay_last_group(self, grads, accumulate=False):
+        """Measurement hook: run the deferred per-Gaussian backward of the most recent group again on the current
+        stream (its per-view accumulators and geometry are still in the slots until the next step).  With
+        accumulate=False `grads` ends up as a one-group step left it.  Returns the radii tensors of the group."""
+        group = getattr(self, "last_group", None)
+        if not group:
+            raise RuntimeError("no deferred group to replay (fuse_backward <= 1, or no step with a backward yet)")
+        refs = [_view_ref(sl.inp, sl.geom, sl.radii, sl.accum, grads.get("means2D")) for sl in group]
+        _preprocess_views(_abi.lib(), group[0].inp, refs, accumulate, grads, torch.cuda.current_stream(self.dev))
+        return [sl.radii for sl in group]
 
     # ---- public -------------------------------------------------------------------------------------------
     def step(self, settings, dL_fn, grads, means3D, opacities, shs=None, colors_precomp=None, scales=None,

@@ -394,6 +394,45 @@ def fetch_u32(torch, wl, name):
     return buf.cpu().numpy().view(np.uint32)
 
 
+def fused_backward_leg(torch, wl, hbm_peak, reps=10):
+    """The pipelined step (`value`) does the per-Gaussian backward once per group of views
+    (gsr_backward_preprocess_views) instead of once per view: time that launch alone on the last group (CUDA events,
+    one stream) and state the bytes it must move."""
+    wl.step(None)  # a pipelined step: leaves the last group's accumulators / geometry in the pipeline's slots
+    vp = wl.vp
+    if vp is None or not getattr(vp, "last_group", None):
+        return None
+    radii = vp.replay_last_group(wl.grads)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        vp.replay_last_group(wl.grads)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    n = len(radii)
+    live = torch.stack([r > 0 for r in radii])
+    v_sum, v_any = int(live.sum().item()), int(live.any(0).sum().item())
+    P = wl.P
+    # per Gaussian some view rendered: mean 12 + rotation 16 + scale 12 + SH row 192 read once, gradient rows 236 written
+    # once; per (Gaussian, view that rendered it): accumulator row 48 + conic 16 + clamp bits 1; radii of every view 4 n P
+    own = v_any * (12 + 16 + 12 + 192 + 236) + v_sum * (48 + 16 + 1) + 4 * n * P + (P - v_any) * 236
+    per_view_alg = 559 * (v_sum / n) + 300 * P  # SURVEY 8(d) formula of the per-view kernel it replaces
+    dram = None
+    try:
+        dram = json.load(open(os.path.join(ROOT, "profiles", "r2b_traffic.json")))["preprocess_bwd_views"]
+    except Exception:
+        pass
+    return {"ms_per_launch": ms, "views_per_launch": n, "ms_per_view": ms / n, "alg_own_bytes": int(own),
+            "dram_bytes": dram.get("dram_bytes_per_launch") if dram else None,
+            "dram_bytes_source": "profiles/r2b_traffic.json (ncu --set full, same workload)" if dram else None,
+            "ncu_issue_active_pct": dram.get("issue_active_pct") if dram else None,
+            "hbm_gbs": own / (ms * 1e-3) / 1e9, "hbm_frac": own / (ms * 1e-3) / 1e9 / hbm_peak,
+            "bytes_of_the_per_view_kernels_it_replaces": int(per_view_alg * n),
+            "what": "gsr_backward_preprocess_views: attributes read once and gradient rows written once per group of views"}
+
+
 def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
     """Per-stage average duration (CUDA events on the launching stream, gsr_profile_*) and roofline
     fractions from the algorithmic bytes of SURVEY.md section 8(d) / DESIGN.md."""
@@ -435,7 +474,7 @@ def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
     alg_own["sort"] = (4 + 16 * 4) * P + 16 * tile_passes * L            # depth sort + tile sort
     alg_own["tile_ranges"] = 4 * L + 8 * tiles
     cap = {}
-    for nm in ("r2_traffic.json", "r1_traffic.json"):  # committed `ncu --set full` capture of one view (tools/ncu_traffic.py)
+    for nm in ("r2b_traffic.json", "r2_traffic.json", "r1_traffic.json"):  # committed `ncu --set full` capture of one view (tools/ncu_traffic.py)
         try:
             cap = json.load(open(os.path.join(ROOT, "profiles", nm)))
             cap["_file"] = "profiles/" + nm
@@ -626,6 +665,9 @@ def run_gsr(args):
 
     # ---- per-stage timing (rank 0 reports; every rank runs it to stay in lock-step)
     stages, counts = stage_table(torch, wl, max(1, min(args.steps, 5)), hbm_peak, sm_max)
+    fused = fused_backward_leg(torch, wl, hbm_peak) if args.api == "views" and wl.overlap else None
+    if fused:
+        stages["preprocess_bwd"]["fused_views"] = fused
     if dist is not None:
         dist.barrier()
 
