@@ -173,6 +173,66 @@ int gsr_forward_geometry(const gsr_inputs* in, void* geom, int32_t* radii, void*
   return GSR_OK;
 }
 
+int gsr_forward_preprocess_views(const gsr_inputs* in, int32_t n_views, const gsr_view_fwd* views, void* stream) {
+  if (!in) { set_error("inputs is NULL"); return GSR_ERR_INVALID; }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (in->P < 0) { set_error("bad size P=%d", in->P); return GSR_ERR_INVALID; }
+  if (in->P == 0 || n_views == 0) return GSR_OK;
+  if (n_views < 0 || n_views > GSR_MAX_FUSED_VIEWS || !views) {
+    set_error("forward_preprocess_views: 1..%d views per call, got %d", GSR_MAX_FUSED_VIEWS, n_views); return GSR_ERR_INVALID;
+  }
+  if (in->raw_params || in->shs_rest || in->K > 0 || in->prefiltered) {
+    set_error("forward_preprocess_views: raw_params / shs_rest / object channels / prefiltered are not supported");
+    return GSR_ERR_INVALID;
+  }
+  if (!in->means3D || !in->opacities || (in->shs == nullptr) == (in->colors_precomp == nullptr)) {
+    set_error("Please provide excatly one of either SHs or precomputed colors!"); return GSR_ERR_INVALID;
+  }
+  const bool sr = in->scales != nullptr && in->rotations != nullptr;
+  if (sr == (in->cov3D_precomp != nullptr) || ((in->scales != nullptr) != (in->rotations != nullptr))) {
+    set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    return GSR_ERR_INVALID;
+  }
+  if (in->shs && (in->M < 1 || in->D < 0 || in->D > 3 || (in->D + 1) * (in->D + 1) > in->M)) {
+    set_error("SH degree %d needs %d coefficients, M=%d", in->D, (in->D + 1) * (in->D + 1), in->M); return GSR_ERR_INVALID;
+  }
+  if (misaligned16(in->shs) || misaligned16(in->rotations)) { set_error("shs and rotations must be 16-byte aligned"); return GSR_ERR_INVALID; }
+  for (int v = 0; v < n_views; v++) {
+    const gsr_view_fwd& r = views[v];
+    if (!r.viewmatrix || !r.projmatrix || !r.campos || !r.geom || !r.radii || r.W <= 0 || r.H <= 0 ||
+        r.W > 65535 * TILE_X || r.H > 65535 * TILE_Y || misaligned16(r.geom)) {
+      set_error("forward_preprocess_views: view %d has a NULL / misaligned pointer or a bad size", v); return GSR_ERR_INVALID;
+    }
+  }
+  { StageScope ps(ST_PREPROCESS_FWD, st); GSR_TRY(launch_preprocess_fwd_views(*in, n_views, views, st)); }
+  return debug_sync(in, st, "preprocess_views");
+}
+
+int gsr_forward_order(const gsr_inputs* in, void* geom, void* scratch, size_t scratch_bytes,
+                      uint32_t* num_rendered_dev, uint32_t* num_rendered_host, void* stream) {
+  if (!in) { set_error("inputs is NULL"); return GSR_ERR_INVALID; }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!geom || !scratch || !num_rendered_dev) { set_error("NULL buffer"); return GSR_ERR_INVALID; }
+  if (in->P < 0) { set_error("bad size P=%d", in->P); return GSR_ERR_INVALID; }
+  if (scratch_bytes < Scratch(nullptr, in->P, 0).bytes) { set_error("scratch too small"); return GSR_ERR_CAPACITY; }
+  if (in->P == 0) {
+    GSR_CUDA_CHECK(cudaMemsetAsync(num_rendered_dev, 0, 4, st));
+    if (num_rendered_host) *num_rendered_host = 0;
+    return GSR_OK;
+  }
+  Geom g(geom, in->P);
+  Scratch s(scratch, in->P, 0);
+  GSR_CUDA_CHECK(cudaMemsetAsync(s.scan_status, 0, s.scan_zero_bytes, st));
+  // the depth keys were left in the view's offsets_sorted array (gsr_forward_preprocess_views); 4 passes bring the
+  // sorted keys back there and the order into geom.perm; the scan then overwrites offsets_sorted with its result
+  { StageScope ps(ST_SORT, st);
+    GSR_TRY(launch_sort_pairs_pingpong_u32(g.offsets_sorted, g.perm, s.dkeys_b, s.dvals_b, in->P, nullptr,
+                                           make_sort_plan(in->P, 32, 4), s.sort_temp, false, true, st)); }
+  GSR_TRY(debug_sync(in, st, "depth_sort"));
+  { StageScope ps(ST_DUPLICATE, st); GSR_TRY(launch_sorted_scan(in->P, g, s, num_rendered_dev, num_rendered_host, st)); }
+  return debug_sync(in, st, "sorted_scan");
+}
+
 // L = capacity of point_list / the tile-sort buffers in pairs.  n_dev == nullptr: L is also the exact pair count
 // (the host read it back).  n_dev != nullptr: the count is read on the device (speculative launch, the host has not
 // seen it yet); if it exceeds L the result is incomplete -- never out of bounds -- and the caller redoes the call.

@@ -257,6 +257,7 @@ __device__ __forceinline__ float sh_coeff(const gsr_inputs& in, size_t idx, int 
 // ---- stage launchers (each returns a gsr_status) ---------------------------------------------
 int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch& s, uint32_t* num_rendered_dev,
                           cudaStream_t st);
+int launch_preprocess_fwd_views(const gsr_inputs& in, int n_views, const gsr_view_fwd* views, cudaStream_t st);
 int launch_sorted_scan(int P, const Geom& g, Scratch& s, uint32_t* num_rendered_dev, uint32_t* num_rendered_host,
                        cudaStream_t st);
 int launch_index_scan(int P, const Geom& g, Scratch& s, uint32_t* out, cudaStream_t st);

@@ -302,6 +302,159 @@ preprocess_fwd_kernel(gsr_inputs in, Geom g, int32_t* __restrict__ radii, uint32
 
 }
 
+// ---- several views in one pass (new; no counterpart in the reference, whose preprocessCUDA runs once per camera) ----
+// A multi-camera step renders the SAME Gaussians from several cameras.  Per camera the kernel above reads 236 bytes of
+// attributes per Gaussian (192 of them the SH row) and writes 89; here a thread reads its Gaussian's attributes once,
+// builds the 3D covariance once and loops over the cameras, writing each camera's geometry state.  The per-view
+// arithmetic is the block above, statement for statement (same helpers, same dataflow), so every per-view output is
+// bit-identical to the single-view kernel's (tests/test_gpu_views_fused.py compares the buffers byte for byte).
+// Depth keys go to the view's own offsets_sorted array (free until the depth-order scan overwrites it), from where
+// gsr_forward_order sorts them.  Standard inputs only (no raw_params / shs_rest / prefiltered).
+constexpr int PV_MAX = GSR_MAX_FUSED_VIEWS;
+struct FwdViewDev {
+  float* depths; float2* means2D; float4* conic_opacity; float4* rgb_thr; float* cov3D; uint8_t* clamped;
+  uint32_t* tiles_touched; ushort4* rects; uint32_t* dkeys; int32_t* radii;
+  const float* viewmatrix; const float* projmatrix; const float* campos;
+  float tanfovx, tanfovy;
+  int W, H;
+};
+struct FwdViewsDev {
+  int n;
+  FwdViewDev v[PV_MAX];
+};
+struct FwdViewShared {
+  FwdViewDev d;
+  Cam cam;
+};
+
+// Measured on C2, 8 views per launch: SH row kept in registers across the views (121 registers, two resident blocks)
+// 318 us; re-read per view from L1 / L2 at three resident blocks (80 registers) 420 us, at four 466 us.
+#ifndef GSR_PV_NO_SH_CACHE
+#define GSR_PV_SH_CACHE 1
+#endif
+#ifndef GSR_PV_MINBLOCKS
+#define GSR_PV_MINBLOCKS 2
+#endif
+__global__ void __launch_bounds__(PRE_THREADS, GSR_PV_MINBLOCKS)
+preprocess_fwd_views_kernel(gsr_inputs in, FwdViewsDev fv) {
+  __shared__ FwdViewShared sv[PV_MAX];
+  const int tid = threadIdx.x, nv = fv.n;
+#pragma unroll
+  for (int v = 0; v < PV_MAX; v++) {
+    if (v < nv) {
+      if (tid == 0) sv[v].d = fv.v[v];
+      if (tid < 16) { sv[v].cam.view[tid] = fv.v[v].viewmatrix[tid]; sv[v].cam.proj[tid] = fv.v[v].projmatrix[tid]; }
+      if (tid < 3) sv[v].cam.campos[tid] = fv.v[v].campos[tid];
+    }
+  }
+  __syncthreads();
+  const int idx = (int)(blockIdx.x * PRE_THREADS + tid);
+  if (idx >= in.P) return;
+
+  // view-independent attributes, read once
+  const float px = in.means3D[3 * idx], py = in.means3D[3 * idx + 1], pz = in.means3D[3 * idx + 2];
+  float c3[6];
+  if (in.cov3D_precomp) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) c3[k] = in.cov3D_precomp[6 * (size_t)idx + k];
+  } else {
+    const float3 s_in = make_float3(in.scales[3 * idx], in.scales[3 * idx + 1], in.scales[3 * idx + 2]);
+    const float4 q_in = reinterpret_cast<const float4*>(in.rotations)[idx];
+    covariance3d(s_in, in.scale_modifier, q_in, c3);
+  }
+  const float op = in.opacities[idx];
+  const float thr = -__logf(255.0f * op) - 1e-4f;
+#ifdef GSR_PV_SH_CACHE
+  float shv[48];  // the SH row, read at the first view that renders the Gaussian and kept across the loop
+  bool have_sh = false;
+#endif
+
+  for (int v = 0; v < nv; v++) {
+    const FwdViewShared& S = sv[v];
+    const int W = S.d.W, H = S.d.H;
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    uint32_t touched = 0;
+    int radius = 0;
+    ushort4 rect = make_ushort4(0, 0, 0, 0);
+    const float depth = affine_row(S.cam.view, 2, px, py, pz);
+    if (depth > 0.2f) {
+      const float hx = affine_row(S.cam.proj, 0, px, py, pz);
+      const float hy = affine_row(S.cam.proj, 1, px, py, pz);
+      const float hw = affine_row(S.cam.proj, 3, px, py, pz);
+      const float p_w = frcp(add(hw, 0.0000001f));
+      const float ndc_x = mul(hx, p_w), ndc_y = mul(hy, p_w);
+      if (!in.cov3D_precomp) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) S.d.cov3D[6 * (size_t)idx + k] = c3[k];
+      }
+      const float fy = fdiv((float)H, mul(2.0f, S.d.tanfovy)), fx = fdiv((float)W, mul(2.0f, S.d.tanfovx));
+      const float3 cov = covariance2d(px, py, pz, fx, fy, S.d.tanfovx, S.d.tanfovy, c3, S.cam.view);
+      const float det = sub(mul(cov.x, cov.z), mul(cov.y, cov.y));
+      if (det != 0.0f) {
+        const float det_inv = frcp(det);
+        const float mid = mul(add(cov.x, cov.z), 0.5f);
+        const float disc = fsqrt(fmaxf(sub(mul(mid, mid), det), 0.1f));
+        const float lam = fmaxf(add(mid, disc), sub(mid, disc));
+        const float my_radius = ceilf(mul(fsqrt(lam), 3.0f));
+        const float pix_x = (float)__dmul_rn(__fma_rn(__dadd_rn((double)ndc_x, 1.0), (double)W, -1.0), 0.5);
+        const float pix_y = (float)__dmul_rn(__fma_rn(__dadd_rn((double)ndc_y, 1.0), (double)H, -1.0), 0.5);
+        const int ir = (int)my_radius;
+        const float fr = (float)ir;
+        const int x0 = min(gx, max(0, (int)mul(sub(pix_x, fr), 0.0625f)));
+        const int y0 = min(gy, max(0, (int)mul(sub(pix_y, fr), 0.0625f)));
+        const int x1 = min(gx, max(0, (int)mul(add(add(add(pix_x, fr), 16.0f), -1.0f), 0.0625f)));
+        const int y1 = min(gy, max(0, (int)mul(add(add(add(pix_y, fr), 16.0f), -1.0f), 0.0625f)));
+        const uint32_t area = (uint32_t)(x1 - x0) * (uint32_t)(y1 - y0);
+        if (area != 0) {
+          float rgb[3];
+          uint8_t cbits = 0;
+          if (in.colors_precomp) {
+            rgb[0] = in.colors_precomp[3 * (size_t)idx];
+            rgb[1] = in.colors_precomp[3 * (size_t)idx + 1];
+            rgb[2] = in.colors_precomp[3 * (size_t)idx + 2];
+          } else if (in.M == 16) {
+#ifdef GSR_PV_SH_CACHE
+            if (!have_sh) {  // the SH row is read at the first view that renders this Gaussian and kept
+#else
+            // (variant, slower: the SH row fetched again for every view that renders the Gaussian, from L1 / L2 after
+            // the first time; fewer registers, three resident blocks)
+            float shv[48];
+            {
+#endif
+              const float4* sp = reinterpret_cast<const float4*>(in.shs) + (size_t)idx * 12;
+              const int nload = in.D >= 3 ? 12 : (in.D == 2 ? 7 : (in.D == 1 ? 3 : 1));
+#pragma unroll
+              for (int k = 0; k < 12; k++) {
+                float4 t = k < nload ? __ldg(sp + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                shv[4 * k] = t.x; shv[4 * k + 1] = t.y; shv[4 * k + 2] = t.z; shv[4 * k + 3] = t.w;
+              }
+#ifdef GSR_PV_SH_CACHE
+              have_sh = true;
+#endif
+            }
+            sh_to_rgb(in.D, px, py, pz, S.cam.campos, [&](int i) { return shv[i]; }, rgb, cbits);
+          } else {
+            const float* sp = in.shs + (size_t)idx * in.M * 3;
+            sh_to_rgb(in.D, px, py, pz, S.cam.campos, [&](int i) { return __ldg(sp + i); }, rgb, cbits);
+          }
+          S.d.depths[idx] = depth;
+          S.d.means2D[idx] = make_float2(pix_x, pix_y);
+          S.d.conic_opacity[idx] = make_float4(mul(cov.z, det_inv), mul(det_inv, -cov.y), mul(cov.x, det_inv), op);
+          S.d.rgb_thr[idx] = make_float4(rgb[0], rgb[1], rgb[2], thr);
+          S.d.clamped[idx] = cbits;
+          radius = ir;
+          rect = make_ushort4((unsigned short)x0, (unsigned short)y0, (unsigned short)x1, (unsigned short)y1);
+          touched = area;
+        }
+      }
+    }
+    S.d.radii[idx] = radius;
+    S.d.tiles_touched[idx] = touched;
+    S.d.rects[idx] = rect;
+    S.d.dkeys[idx] = touched ? __float_as_uint(depth) : 0xffffffffu;
+  }
+}
+
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
                                     uint8_t* __restrict__ present) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -323,6 +476,26 @@ int launch_preprocess_fwd(const gsr_inputs& in, Geom& g, int32_t* radii, Scratch
   else
     preprocess_fwd_kernel<false><<<nblocks, PRE_THREADS, 0, st>>>(in, g, radii, s.flags, s.dkeys_a);
   GSR_LAUNCH_CHECK("preprocess_fwd_kernel");
+  return GSR_OK;
+}
+
+int launch_preprocess_fwd_views(const gsr_inputs& in, int n_views, const gsr_view_fwd* views, cudaStream_t st) {
+  FwdViewsDev fv;
+  fv.n = n_views;
+  for (int v = 0; v < n_views; v++) {
+    const gsr_view_fwd& r = views[v];
+    Geom g(r.geom, in.P);
+    GSR_CUDA_CHECK(cudaMemsetAsync(g.giant_count, 0, sizeof(uint32_t), st));
+    FwdViewDev& d = fv.v[v];
+    d.depths = g.depths; d.means2D = g.means2D; d.conic_opacity = g.conic_opacity; d.rgb_thr = g.rgb_thr;
+    d.cov3D = g.cov3D; d.clamped = g.clamped; d.tiles_touched = g.tiles_touched; d.rects = g.rects;
+    d.dkeys = g.offsets_sorted; d.radii = r.radii;
+    d.viewmatrix = r.viewmatrix; d.projmatrix = r.projmatrix; d.campos = r.campos;
+    d.tanfovx = r.tanfovx; d.tanfovy = r.tanfovy; d.W = r.W; d.H = r.H;
+  }
+  const int nblocks = (in.P + PRE_THREADS - 1) / PRE_THREADS;
+  preprocess_fwd_views_kernel<<<nblocks, PRE_THREADS, 0, st>>>(in, fv);
+  GSR_LAUNCH_CHECK("preprocess_fwd_views_kernel");
   return GSR_OK;
 }
 

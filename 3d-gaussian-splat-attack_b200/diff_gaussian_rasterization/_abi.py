@@ -39,6 +39,15 @@ class GsrViewRef(C.Structure):
     ]
 
 
+class GsrViewFwd(C.Structure):
+    """struct gsr_view_fwd (include/gsr_b200.h): one view of the multi-view forward preprocess."""
+    _fields_ = [
+        ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("W", C.c_int32), ("H", C.c_int32),
+        ("geom", C.c_void_p), ("radii", C.c_void_p),
+    ]
+
+
 EXPORTS = {
     # name: (restype, argtypes)
     "gsr_abi_version": (C.c_int, []),
@@ -71,6 +80,9 @@ EXPORTS = {
     "gsr_backward_accumulate_phase": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                                 C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p] + [C.c_void_p] * 8 +
                                       [C.c_int32, C.c_void_p]),
+    "gsr_forward_preprocess_views": (C.c_int, [C.POINTER(GsrInputs), C.c_int32, C.POINTER(GsrViewFwd), C.c_void_p]),
+    "gsr_forward_order": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
     "gsr_view_accum_bytes": (C.c_size_t, [C.c_int32]),
     "gsr_backward_blend_view": (C.c_int, [C.POINTER(GsrInputs), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_void_p]),

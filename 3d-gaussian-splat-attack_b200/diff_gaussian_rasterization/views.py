@@ -19,7 +19,7 @@ import torch
 from . import _abi
 from . import _f32c, _make_inputs, _ptr, _run_forward, _state
 
-__all__ = ["ViewState", "forward_view", "backward_view", "backward_views", "ViewPipeline", "GRAD_KEYS"]
+__all__ = ["ViewState", "forward_view", "forward_views", "backward_view", "backward_views", "ViewPipeline", "GRAD_KEYS"]
 
 # gradient buffers backward_view() accepts, named after GaussianRasterizer.forward's arguments
 GRAD_KEYS = ("means3D", "means2D", "opacities", "shs", "shs_rest", "colors_precomp", "scales", "rotations", "cov3D_precomp")
@@ -71,6 +71,76 @@ def forward_view(raster_settings, means3D, opacities, shs=None, colors_precomp=N
             t["rotations"], t["cov3D_precomp"], None, shs_rest=t["shs_rest"], raw_params=raw_params)
     t["means3D"] = m
     return color, radii, ViewState(raster_settings, P, M, L, t, radii, geom, point_list, image, bool(raw_params))
+
+
+def _view_fwd(inp, geom, radii):
+    r = _abi.GsrViewFwd()
+    r.viewmatrix, r.projmatrix, r.campos = inp.viewmatrix, inp.projmatrix, inp.campos
+    r.tanfovx, r.tanfovy, r.W, r.H = inp.tanfovx, inp.tanfovy, inp.W, inp.H
+    r.geom, r.radii = _ptr(geom), _ptr(radii)
+    return r
+
+
+def forward_views(settings, means3D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                  cov3D_precomp=None):
+    """Render SEVERAL views of the same Gaussians: the per-Gaussian preprocess runs once per group of up to 8 views
+    (gsr_forward_preprocess_views: every Gaussian's attributes are read once instead of once per view), then each
+    view is ordered, binned and blended as forward_view does.  Per view the results are bit-identical to
+    forward_view's.  Returns a list of (color, radii, ViewState), usable with backward_view / backward_views."""
+    if (shs is None) == (colors_precomp is None):
+        raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+    if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+            ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+        raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+    if means3D.ndimension() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+    P = means3D.size(0)
+    if P == 0 or any(rs.prefiltered for rs in settings):
+        return [forward_view(rs, means3D, opacities, shs=shs, colors_precomp=colors_precomp, scales=scales,
+                             rotations=rotations, cov3D_precomp=cov3D_precomp) for rs in settings]
+    dev = means3D.device
+    out = []
+    with torch.no_grad(), torch.cuda.device(dev):
+        lib = _abi.lib()
+        st = _state(dev)
+        stream = torch.cuda.current_stream(dev)
+        sp = C.c_void_p(stream.cuda_stream)
+        t = dict(means3D=_f32c(means3D, "means3D"), shs=_f32c(shs, "shs"),
+                 colors_precomp=_f32c(colors_precomp, "colors_precomp"), opacities=_f32c(opacities, "opacities"),
+                 scales=_f32c(scales, "scales"), rotations=_f32c(rotations, "rotations"),
+                 cov3D_precomp=_f32c(cov3D_precomp, "cov3D_precomp"), shs_rest=None)
+        M = _sh_count(t["shs"], None)
+        F = _abi.MAX_FUSED_VIEWS
+        for c0 in range(0, len(settings), F):
+            group, keep = [], []
+            for rs in settings[c0:c0 + F]:
+                inp = _make_inputs(rs, P, M, 0, t["means3D"], t["shs"], t["colors_precomp"], t["opacities"], t["scales"],
+                                   t["rotations"], t["cov3D_precomp"], None, keep)
+                geom = torch.empty(lib.gsr_geom_bytes(P), dtype=torch.uint8, device=dev)
+                radii = torch.empty((P,), dtype=torch.int32, device=dev)
+                group.append((rs, inp, geom, radii))
+            arr = (_abi.GsrViewFwd * len(group))(*[_view_fwd(inp, geom, radii) for _, inp, geom, radii in group])
+            _abi.check(lib.gsr_forward_preprocess_views(C.byref(group[0][1]), len(group), arr, sp),
+                       "forward_preprocess_views")
+            for rs, inp, geom, radii in group:
+                H, W = int(rs.image_height), int(rs.image_width)
+                image = torch.empty(lib.gsr_image_bytes(W, H), dtype=torch.uint8, device=dev)
+                color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+                scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, 0, W, H))
+                _abi.check(lib.gsr_forward_order(C.byref(inp), _ptr(geom), _ptr(scratch), scratch.numel(),
+                                                 _ptr(st.count_dev), C.c_void_p(st.count_host.data_ptr()), sp),
+                           "forward_order")
+                stream.synchronize()  # the duplicate count (reference: rasterizer_impl.cu:281)
+                L = int(st.count_host.item()) & 0xFFFFFFFF
+                point_list = torch.empty((max(L, 1),), dtype=torch.int32, device=dev)
+                scratch = st.ensure_scratch(lib.gsr_scratch_bytes(P, L, W, H))
+                _abi.check(lib.gsr_forward_render(C.byref(inp), _ptr(geom), _ptr(radii), L, _ptr(point_list),
+                                                  _ptr(image), _ptr(scratch), scratch.numel(), _ptr(color), None, sp),
+                           "forward_render")
+                out.append((color, radii, ViewState(rs, P, M, L, t, radii, geom, point_list, image, False)))
+    return out
 
 
 def _check_aligned(name, g):
@@ -278,16 +348,23 @@ class ViewPipeline:
     backward's accumulators.  Results are those of forward_view / backward_view (same kernels, same order of
     accumulation into `grads`)."""
 
-    def __init__(self, device=None, n_slots: int = 3, overlap: bool = True, fuse_backward: int = _abi.MAX_FUSED_VIEWS):
+    def __init__(self, device=None, n_slots: int = 3, overlap: bool = True, fuse_backward: int = _abi.MAX_FUSED_VIEWS,
+                 fuse_forward: bool = True):
         """fuse_backward = F > 1: the per-Gaussian half of the backward (preprocess_bwd) is deferred and done ONCE per
         group of up to F cameras (gsr_backward_preprocess_views: attributes read once, gradient rows written once per
         group instead of once per camera); each slot then keeps its own 48-byte-per-Gaussian accumulator and the ring
-        grows to F + 2 slots.  fuse_backward <= 1: one preprocess_bwd per camera, as backward_view does."""
+        grows to F + 2 slots.  fuse_backward <= 1: one preprocess_bwd per camera, as backward_view does.
+        fuse_forward (with fuse_backward > 1): the per-Gaussian preprocess of a whole group of F cameras is one launch
+        (gsr_forward_preprocess_views: attributes read once per Gaussian instead of once per camera; per-camera results
+        bit-identical), followed per camera by gsr_forward_order; the ring then holds 2 F + 2 slots."""
         if n_slots < 2:
             raise ValueError("n_slots must be >= 2")
         self.fuse = max(1, min(int(fuse_backward), _abi.MAX_FUSED_VIEWS))
+        self.fuse_fwd = bool(fuse_forward) and self.fuse > 1
         if self.fuse > 1:
-            n_slots = max(n_slots, self.fuse + 2)
+            # a group's slots stay in use until its deferred backward has run; with the grouped preprocess the NEXT
+            # group's geometry is written while the current group is still pending
+            n_slots = max(n_slots, (2 * self.fuse if self.fuse_fwd else self.fuse) + 2)
         self.pending = []     # slots whose blend_bwd has been queued and whose per-Gaussian backward is deferred
         self.overwrite_next = False  # the next deferred pass SETS the gradient rows instead of adding to them
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
@@ -315,8 +392,41 @@ class ViewPipeline:
 
     def _geometry(self, slot, rs, t, P, M, grads=None, raw_params=False):
         lib = _abi.lib()
+        G = self._gstream()
+        self._prepare_slot(slot, rs, t, P, M, grads, raw_params)
+        _abi.check(lib.gsr_forward_geometry(C.byref(slot.inp), _ptr(slot.geom), _ptr(slot.radii), _ptr(self.scratch),
+                                            self.scratch.numel(), _ptr(slot.count_dev),
+                                            C.c_void_p(slot.count_host.data_ptr()), C.c_void_p(G.cuda_stream)),
+                   "forward_geometry")
+        slot.ev_geom.record(G)
+
+    def _preprocess_group(self, slots, settings, t, P, M, grads):
+        """Phase 1a of a whole group of cameras in one launch on G (gsr_forward_preprocess_views): attributes read once."""
+        lib = _abi.lib()
+        G = self._gstream()
+        for slot, rs in zip(slots, settings):
+            self._prepare_slot(slot, rs, t, P, M, grads, False)
+        arr = (_abi.GsrViewFwd * len(slots))(*[_view_fwd(sl.inp, sl.geom, sl.radii) for sl in slots])
+        _abi.check(lib.gsr_forward_preprocess_views(C.byref(slots[0].inp), len(slots), arr, C.c_void_p(G.cuda_stream)),
+                   "forward_preprocess_views")
+        self.last_fwd_group = list(slots)  # measurement hook (replay_last_preprocess)
+
+    def _order(self, slot):
+        """Phase 1b of one camera on G: depth order, prefix sum, duplicate count (the rest of gsr_forward_geometry)."""
+        lib = _abi.lib()
+        G = self._gstream()
+        _abi.check(lib.gsr_forward_order(C.byref(slot.inp), _ptr(slot.geom), _ptr(self.scratch), self.scratch.numel(),
+                                         _ptr(slot.count_dev), C.c_void_p(slot.count_host.data_ptr()),
+                                         C.c_void_p(G.cuda_stream)), "forward_order")
+        slot.ev_geom.record(G)
+
+    def _prepare_slot(self, slot, rs, t, P, M, grads=None, raw_params=False):
+        """Buffers and the gsr_inputs of one camera; G waits until the slot's previous user is done with it."""
+        lib = _abi.lib()
         W, H = int(rs.image_width), int(rs.image_height)
         G = self._gstream()
+        if any(sl is slot for sl in self.pending):  # (many cameras without a backward since this one: finish its group first)
+            self._flush_pending(self._step_grads)
         if slot.busy and self.overlap:
             G.wait_event(slot.ev_done)
         sig = (P, W, H)
@@ -332,11 +442,6 @@ class ViewPipeline:
                            t["rotations"], t["cov3D_precomp"], None, keep, shs_rest=t.get("shs_rest"),
                            raw_params=raw_params, dL_dshs_rest=(grads or {}).get("shs_rest"))
         slot.keep, slot.inp = keep, inp
-        _abi.check(lib.gsr_forward_geometry(C.byref(inp), _ptr(slot.geom), _ptr(slot.radii), _ptr(self.scratch),
-                                            self.scratch.numel(), _ptr(slot.count_dev),
-                                            C.c_void_p(slot.count_host.data_ptr()), C.c_void_p(G.cuda_stream)),
-                   "forward_geometry")
-        slot.ev_geom.record(G)
 
     def _binning(self, slot, rs, P):
         lib = _abi.lib()
@@ -431,6 +536,18 @@ class ViewPipeline:
             self.pb_pending = True
         self.pending = []
 
+    def replay_last_preprocess(self):
+        """Measurement hook: the most recent grouped preprocess launch again, on the current stream, after the step
+        has finished (it rewrites the same geometry state; the slots' depth keys are not needed any more)."""
+        group = getattr(self, "last_fwd_group", None)
+        if not group:
+            raise RuntimeError("no grouped preprocess to replay (fuse_forward off, or no step yet)")
+        arr = (_abi.GsrViewFwd * len(group))(*[_view_fwd(sl.inp, sl.geom, sl.radii) for sl in group])
+        _abi.check(_abi.lib().gsr_forward_preprocess_views(
+            C.byref(group[0].inp), len(group), arr, C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)),
+            "forward_preprocess_views")
+        return [sl.radii for sl in group]
+
     def replay_last_group(self, grads, accumulate=False):
         """Measurement hook: run the deferred per-Gaussian backward of the most recent group again on the current
         stream (its per-view accumulators and geometry are still in the slots until the next step).  With
@@ -502,6 +619,7 @@ class ViewPipeline:
                 self.ev_start.record(R)
                 self.G.wait_event(self.ev_start)
             fused = self.fuse > 1 and not raw_params and t["shs_rest"] is None and (M <= 16)
+            self._step_grads = grads
             self.overwrite_next = bool(overwrite) and fused and grads.get("means2D") is None and \
                 any(g is not None for g in grads.values())
             if overwrite and not self.overwrite_next:
@@ -509,12 +627,24 @@ class ViewPipeline:
                     if gbuf is not None:
                         gbuf.zero_()
             ns = len(self.slots)
-            self._geometry(self.slots[0], settings[0], t, P, M, grads, raw_params)
+            fused_fwd = fused and self.fuse_fwd and not any(rs.prefiltered for rs in settings)
+            F = self.fuse
+
+            def geometry(k):  # phase 1 of camera k on G
+                if not fused_fwd:
+                    self._geometry(self.slots[k % ns], settings[k], t, P, M, grads, raw_params)
+                    return
+                if k % F == 0:  # first camera of a group: the whole group's preprocess in one launch
+                    ks = range(k, min(k + F, n))
+                    self._preprocess_group([self.slots[j % ns] for j in ks], [settings[j] for j in ks], t, P, M, grads)
+                self._order(self.slots[k % ns])
+
+            geometry(0)
             self._binning(self.slots[0], settings[0], P)
             for k in range(n):
                 slot = self.slots[k % ns]
                 if k + 1 < n:
-                    self._geometry(self.slots[(k + 1) % ns], settings[k + 1], t, P, M, grads, raw_params)
+                    geometry(k + 1)
                 color = self._blend(slot, settings[k])
                 counts.append(slot.L)
                 with torch.enable_grad():

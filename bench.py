@@ -433,6 +433,35 @@ def fused_backward_leg(torch, wl, hbm_peak, reps=10):
             "what": "gsr_backward_preprocess_views: attributes read once and gradient rows written once per group of views"}
 
 
+def fused_forward_leg(torch, wl, hbm_peak, reps=10):
+    """The grouped preprocess of the pipelined step (gsr_forward_preprocess_views) timed alone on the last group."""
+    vp = wl.vp
+    if vp is None or not getattr(vp, "last_fwd_group", None):
+        return None
+    torch.cuda.synchronize()
+    radii = vp.replay_last_preprocess()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        vp.replay_last_preprocess()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    n = len(radii)
+    live = torch.stack([r > 0 for r in radii])
+    v_sum, v_any = int(live.sum().item()), int(live.any(0).sum().item())
+    P = wl.P
+    # attributes once per Gaussian (mean 12, scale 12, rotation 16, opacity 4; SH row 192 if some view renders it);
+    # per (Gaussian, view): radii 4 + tiles 4 + rect 8 + depth key 4 always, 69 more of geometry state when rendered
+    own = P * 44 + v_any * 192 + n * P * 20 + v_sum * 69
+    return {"ms_per_launch": ms, "views_per_launch": n, "ms_per_view": ms / n, "alg_own_bytes": int(own),
+            "hbm_gbs": own / (ms * 1e-3) / 1e9, "hbm_frac": own / (ms * 1e-3) / 1e9 / hbm_peak,
+            "bytes_of_the_per_view_kernels_it_replaces": int(311 * v_sum + 20 * (n * P - v_sum)),
+            "what": "gsr_forward_preprocess_views: attributes read once per Gaussian for a group of views; per-view "
+                    "outputs bit-identical to preprocess_fwd_kernel's"}
+
+
 def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
     """Per-stage average duration (CUDA events on the launching stream, gsr_profile_*) and roofline
     fractions from the algorithmic bytes of SURVEY.md section 8(d) / DESIGN.md."""
@@ -668,6 +697,9 @@ def run_gsr(args):
     fused = fused_backward_leg(torch, wl, hbm_peak) if args.api == "views" and wl.overlap else None
     if fused:
         stages["preprocess_bwd"]["fused_views"] = fused
+        ff = fused_forward_leg(torch, wl, hbm_peak)
+        if ff:
+            stages["preprocess_fwd"]["fused_views"] = ff
     if dist is not None:
         dist.barrier()
 

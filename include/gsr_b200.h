@@ -188,6 +188,27 @@ int gsr_backward_preprocess_views(const gsr_inputs* in, int32_t n_views, const g
                                   int32_t accumulate, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
                                   float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* stream);
 
+/* ---- forward phase 1 of SEVERAL views of the same Gaussians (new; the reference's preprocessCUDA, forward.cu:155-256,
+ *      runs once per camera and re-reads every Gaussian's attributes -- 236 bytes, 192 of them the SH row -- each time).
+ *      gsr_forward_preprocess_views reads the attributes once per Gaussian and writes the geometry state and radii of
+ *      up to GSR_MAX_FUSED_VIEWS views (`views_host` is a HOST array); per view the arithmetic and therefore every
+ *      output is bit-identical to gsr_forward_geometry's.  gsr_forward_order then finishes phase 1 of ONE view (depth
+ *      order, prefix sum, duplicate count -- the rest of gsr_forward_geometry) and is followed by phase 2 as usual.
+ *      `in` supplies the scene (camera fields ignored by the first call; P by the second).  Standard inputs only:
+ *      raw_params / shs_rest / prefiltered / K > 0 return GSR_ERR_INVALID. ---- */
+typedef struct gsr_view_fwd {
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  float tanfovx, tanfovy;
+  int32_t W, H;
+  void* geom;               /* output: that view's geometry state (gsr_geom_bytes(P))                      */
+  int32_t* radii;           /* output: that view's radii (P)                                               */
+} gsr_view_fwd;
+int gsr_forward_preprocess_views(const gsr_inputs* in, int32_t n_views, const gsr_view_fwd* views_host, void* stream);
+int gsr_forward_order(const gsr_inputs* in, void* geom, void* scratch, size_t scratch_bytes,
+                      uint32_t* num_rendered_dev, uint32_t* num_rendered_host, void* stream);
+
 /* ---- markVisible (rasterizer_impl.cu:141-153, checkFrustum :54-66); present is (P) bytes ---- */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);

@@ -207,3 +207,100 @@ def test_view_pipeline_fused_and_unfused_agree(fuse):
     for k in g0:
         ok, worst = h.grad_close(g1[k].cpu().numpy(), g0[k].cpu().numpy(), **TOL)
         assert ok, (fuse, "means2D run", k, worst)
+
+
+def test_forward_views_is_bit_identical_to_forward_view():
+    """gsr_forward_preprocess_views + gsr_forward_order against gsr_forward_geometry: the whole geometry state, radii,
+    duplicate count, point list and image of every view, byte for byte; 11 views = a group of 8 and a group of 3."""
+    from diff_gaussian_rasterization import views
+    s = h.make_scene("small")
+    t = h.scene_tensors(s, requires_grad=False)
+    settings = _views_of(s, 11, W=320, H=240)
+    kw = dict(shs=t["shs"], scales=t["scales"], rotations=t["rotations"])
+    got = views.forward_views(settings, t["means3D"], t["opacities"], **kw)
+    assert len(got) == len(settings)
+    for rs, (img, radii, st) in zip(settings, got):
+        ref_img, ref_radii, ref_st = views.forward_view(rs, t["means3D"], t["opacities"], **kw)
+        assert st.L == ref_st.L
+        assert torch.equal(radii, ref_radii)
+        assert torch.equal(img, ref_img)
+        assert torch.equal(st.point_list[: st.L], ref_st.point_list[: st.L])
+        P, L, W, H = st.P, st.L, 320, 240
+        for name, dt in (("depths", np.float32), ("means2D", np.float32), ("conic_opacity", np.float32), ("rgb", np.float32),
+                         ("clamped", np.uint8), ("tiles_touched", np.uint32), ("rects", np.uint16), ("perm", np.uint32),
+                         ("offsets_sorted", np.uint32), ("cov3D", np.float32), ("n_contrib", np.uint32),
+                         ("final_T", np.float32), ("ranges", np.uint32)):
+            a = h.gsr_fetch(name, dt, P, W, H, L, st.geom, st.image, None, st.point_list)
+            b = h.gsr_fetch(name, dt, P, W, H, L, ref_st.geom, ref_st.image, None, ref_st.point_list)
+            if name in ("depths", "means2D", "conic_opacity", "rgb", "clamped", "cov3D"):
+                vis = (ref_radii > 0).cpu().numpy()  # rows of culled Gaussians are never written (either path)
+                k = a.size // P
+                a, b = a.reshape(P, k)[vis], b.reshape(P, k)[vis]
+            assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), name
+    # gradients through the states of the grouped forward
+    rng = np.random.default_rng(4)
+    dLs = [torch.from_numpy(rng.standard_normal((3, 240, 320)).astype(np.float32)).cuda() for _ in settings]
+    g1 = {k: torch.zeros_like(v) for k, v in t.items()}
+    views.backward_views([st for _, _, st in got], dLs, g1, accumulate=False)
+    states = _forward_all(settings, t, **kw)
+    g0, _ = _per_view_reference(states, dLs, t)
+    for k in g0:
+        ok, worst = h.grad_close(g1[k].cpu().numpy(), g0[k].cpu().numpy(), **TOL)
+        assert ok, (k, worst)
+
+
+def test_forward_views_precomputed_inputs_and_low_sh_degree():
+    from diff_gaussian_rasterization import views
+    sc, kw, gold = h.golden_case("tiny_precomp")
+    t = h.scene_tensors(sc, requires_grad=False)
+    col = torch.from_numpy(kw["colors_precomp"]).cuda()
+    cov = torch.from_numpy(kw["cov3D_precomp"]).cuda()
+    settings = _views_of(sc, 3, W=sc["cam"]["image_width"], H=sc["cam"]["image_height"])
+    for (img, radii, st), rs in zip(views.forward_views(settings, t["means3D"], t["opacities"], colors_precomp=col,
+                                                        cov3D_precomp=cov), settings):
+        ref_img, ref_radii, _ = views.forward_view(rs, t["means3D"], t["opacities"], colors_precomp=col, cov3D_precomp=cov)
+        assert torch.equal(img, ref_img) and torch.equal(radii, ref_radii)
+    sc, kw, gold = h.golden_case("tiny_sh1_bg")
+    t = h.scene_tensors(sc, requires_grad=False)
+    settings = _views_of(sc, 3, W=sc["cam"]["image_width"], H=sc["cam"]["image_height"])
+    for shs in (t["shs"], t["shs"][:, :4, :].contiguous()):
+        kw2 = dict(shs=shs, scales=t["scales"], rotations=t["rotations"])
+        for (img, radii, st), rs in zip(views.forward_views(settings, t["means3D"], t["opacities"], **kw2), settings):
+            ref_img, ref_radii, _ = views.forward_view(rs, t["means3D"], t["opacities"], **kw2)
+            assert torch.equal(img, ref_img) and torch.equal(radii, ref_radii), tuple(shs.shape)
+
+
+@pytest.mark.parametrize("fuse_forward", [True, False])
+def test_view_pipeline_grouped_preprocess_images_bit_identical(fuse_forward):
+    """ViewPipeline with the grouped preprocess: images bit-identical to forward_view, gradients equal to per-view
+    sums; 19 cameras (more than the 18 slots of the ring), three steps, a camera without a backward."""
+    from diff_gaussian_rasterization import views
+    s = h.make_scene("small")
+    t = h.scene_tensors(s, requires_grad=False)
+    settings = _views_of(s, 19, W=320, H=240)
+    rng = np.random.default_rng(23)
+    dLs = [torch.from_numpy(rng.standard_normal((3, 240, 320)).astype(np.float32)).cuda() for _ in settings]
+    kw = dict(shs=t["shs"], scales=t["scales"], rotations=t["rotations"])
+    ref_imgs, states = [], []
+    for rs in settings:
+        img, radii, st = views.forward_view(rs, t["means3D"], t["opacities"], **kw)
+        ref_imgs.append(img); states.append(st)
+    vp = views.ViewPipeline(fuse_forward=fuse_forward)
+    for rep in range(3):
+        skip = {5, 6} if rep == 1 else set()
+        keep = [i for i in range(len(settings)) if i not in skip]
+        want, _ = _per_view_reference([states[i] for i in keep], [dLs[i] for i in keep], t)
+        got = {k: torch.full_like(v, 2.0) for k, v in t.items()}
+        imgs = []
+
+        def dL_fn(img, k):
+            imgs.append(img.clone())
+            return None if k in skip else dLs[k]
+        counts = vp.step(settings, dL_fn, got, t["means3D"], t["opacities"], overwrite=True, **kw)
+        torch.cuda.synchronize()
+        assert counts == [st.L for st in states]
+        for a, b in zip(imgs, ref_imgs):
+            assert torch.equal(a, b)
+        for k in want:
+            ok, worst = h.grad_close(got[k].cpu().numpy(), want[k].cpu().numpy(), **TOL)
+            assert ok, (fuse_forward, rep, k, worst)
