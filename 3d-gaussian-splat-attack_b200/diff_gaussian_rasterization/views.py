@@ -349,14 +349,17 @@ class ViewPipeline:
     accumulation into `grads`)."""
 
     def __init__(self, device=None, n_slots: int = 3, overlap: bool = True, fuse_backward: int = _abi.MAX_FUSED_VIEWS,
-                 fuse_forward: bool = True):
+                 fuse_forward: bool = True, parallel_order: bool = False):
         """fuse_backward = F > 1: the per-Gaussian half of the backward (preprocess_bwd) is deferred and done ONCE per
         group of up to F cameras (gsr_backward_preprocess_views: attributes read once, gradient rows written once per
         group instead of once per camera); each slot then keeps its own 48-byte-per-Gaussian accumulator and the ring
         grows to F + 2 slots.  fuse_backward <= 1: one preprocess_bwd per camera, as backward_view does.
         fuse_forward (with fuse_backward > 1): the per-Gaussian preprocess of a whole group of F cameras is one launch
         (gsr_forward_preprocess_views: attributes read once per Gaussian instead of once per camera; per-camera results
-        bit-identical), followed per camera by gsr_forward_order; the ring then holds 2 F + 2 slots."""
+        bit-identical), followed per camera by gsr_forward_order; the ring then holds 2 F + 2 slots.
+        parallel_order (experiment, off): the depth orders of a group's cameras side by side on F extra streams.
+        Measured on C2: 967 -> 969 views/s, but with eight more streams the copy streams of pipeline.HostStepPipeline
+        end up sharing hardware queues with compute streams (CUDA_DEVICE_MAX_CONNECTIONS = 8) and `e2e` halves."""
         if n_slots < 2:
             raise ValueError("n_slots must be >= 2")
         self.fuse = max(1, min(int(fuse_backward), _abi.MAX_FUSED_VIEWS))
@@ -374,6 +377,10 @@ class ViewPipeline:
         self.G = torch.cuda.Stream(dev, priority=-1) if overlap else None  # measured: 710 views/s vs 680 at equal priority
         self.B = torch.cuda.Stream(dev, priority=-1) if overlap else None
         self.scratch = torch.empty(0, dtype=torch.uint8, device=dev)
+        n_order = self.fuse if (overlap and self.fuse_fwd and parallel_order) else 0
+        self.O = [torch.cuda.Stream(dev, priority=-1) for _ in range(n_order)]  # ordering streams (grouped preprocess)
+        self.o_scratch = [None] * n_order
+        self.ev_pre = torch.cuda.Event()
         self.ev_start, self.ev_bb, self.ev_pb = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
         self.pb_pending = False
 
@@ -410,15 +417,26 @@ class ViewPipeline:
         _abi.check(lib.gsr_forward_preprocess_views(C.byref(slots[0].inp), len(slots), arr, C.c_void_p(G.cuda_stream)),
                    "forward_preprocess_views")
         self.last_fwd_group = list(slots)  # measurement hook (replay_last_preprocess)
+        if self.overlap:
+            self.ev_pre.record(G)
 
-    def _order(self, slot):
-        """Phase 1b of one camera on G: depth order, prefix sum, duplicate count (the rest of gsr_forward_geometry)."""
+    def _order(self, slot, lane=None):
+        """Phase 1b of one camera: depth order, prefix sum, duplicate count (the rest of gsr_forward_geometry).
+        lane = None: on G with the pipeline's scratch.  lane = i: on the i-th ordering stream with that stream's own
+        scratch -- the depth sorts of a group's cameras are independent and each is latency-bound (one wave of
+        tiles, four dependent launches), so queued side by side their tails and launch gaps fill each other."""
         lib = _abi.lib()
-        G = self._gstream()
-        _abi.check(lib.gsr_forward_order(C.byref(slot.inp), _ptr(slot.geom), _ptr(self.scratch), self.scratch.numel(),
+        if lane is None or not self.overlap:
+            stream, scratch = self._gstream(), self.scratch
+        else:
+            stream = self.O[lane]
+            need = lib.gsr_scratch_bytes(slot.inp.P, 0, slot.inp.W, slot.inp.H)
+            self.o_scratch[lane] = scratch = self._ensure(self.o_scratch[lane], need)
+            stream.wait_event(self.ev_pre)
+        _abi.check(lib.gsr_forward_order(C.byref(slot.inp), _ptr(slot.geom), _ptr(scratch), scratch.numel(),
                                          _ptr(slot.count_dev), C.c_void_p(slot.count_host.data_ptr()),
-                                         C.c_void_p(G.cuda_stream)), "forward_order")
-        slot.ev_geom.record(G)
+                                         C.c_void_p(stream.cuda_stream)), "forward_order")
+        slot.ev_geom.record(stream)
 
     def _prepare_slot(self, slot, rs, t, P, M, grads=None, raw_params=False):
         """Buffers and the gsr_inputs of one camera; G waits until the slot's previous user is done with it."""
@@ -618,7 +636,8 @@ class ViewPipeline:
             if self.overlap:  # whatever produced the inputs on the caller's stream must be visible to G
                 self.ev_start.record(R)
                 self.G.wait_event(self.ev_start)
-            fused = self.fuse > 1 and not raw_params and t["shs_rest"] is None and (M <= 16)
+            # (a single camera gains nothing from the grouped kernels: they run at lower occupancy than the per-view ones)
+            fused = self.fuse > 1 and n > 1 and not raw_params and t["shs_rest"] is None and (M <= 16)
             self._step_grads = grads
             self.overwrite_next = bool(overwrite) and fused and grads.get("means2D") is None and \
                 any(g is not None for g in grads.values())
@@ -637,7 +656,13 @@ class ViewPipeline:
                 if k % F == 0:  # first camera of a group: the whole group's preprocess in one launch
                     ks = range(k, min(k + F, n))
                     self._preprocess_group([self.slots[j % ns] for j in ks], [settings[j] for j in ks], t, P, M, grads)
-                self._order(self.slots[k % ns])
+                if not self.O:
+                    self._order(self.slots[k % ns])
+                elif k % F == 0:  # the group's first camera is ordered at once on G ...
+                    self._order(self.slots[k % ns])
+                elif k % F == 1:  # ... the others side by side on the ordering streams once its binning is queued
+                    for j in range(k, min(k - 1 + F, n)):
+                        self._order(self.slots[j % ns], lane=j % F)
 
             geometry(0)
             self._binning(self.slots[0], settings[0], P)
@@ -666,6 +691,8 @@ class ViewPipeline:
                 ev = torch.cuda.Event()
                 ev.record(self.G)
                 R.wait_event(ev)
+                for o in self.O:  # (every ordering launch was followed by a host wait on its event: already complete)
+                    R.wait_stream(o)
                 if self.pb_pending:
                     R.wait_event(self.ev_pb)
                     self.pb_pending = False

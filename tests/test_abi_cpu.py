@@ -38,6 +38,26 @@ def test_abi_version_and_struct_layout():
     assert _abi.lib().gsr_abi_version() == _abi.ABI_VERSION
     # 8 int32 + 3 float + 1 int32 + 14 pointers
     assert C.sizeof(_abi.GsrInputs) == 8 * 4 + 4 * 4 + 14 * 8
+    # the ctypes mirrors of the multi-view structs against the C compiler's layout of include/gsr_b200.h
+    import subprocess, tempfile, os
+    src = r"""
+#include <stdio.h>
+#include <stddef.h>
+#include "gsr_b200.h"
+int main(void) {
+  printf("%zu %zu %zu %zu %zu %zu %zu\n", sizeof(gsr_inputs), sizeof(gsr_view_ref), offsetof(gsr_view_ref, geom),
+         offsetof(gsr_view_ref, dL_dmean2D), sizeof(gsr_view_fwd), offsetof(gsr_view_fwd, W), offsetof(gsr_view_fwd, radii));
+  return 0;
+}
+"""
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, "l.c"), "w").write(src)
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", os.path.join(d, "l"), os.path.join(d, "l.c")])
+        got = [int(x) for x in subprocess.check_output([os.path.join(d, "l")]).split()]
+    R, F = _abi.GsrViewRef, _abi.GsrViewFwd
+    assert got == [C.sizeof(_abi.GsrInputs), C.sizeof(R), R.geom.offset, R.dL_dmean2D.offset, C.sizeof(F), F.W.offset,
+                   F.radii.offset]
+    assert _abi.MAX_FUSED_VIEWS == 8
 
 
 def test_higher_msb_matches_reference_semantics():
