@@ -421,12 +421,12 @@ def fused_backward_leg(torch, wl, hbm_peak, reps=10):
     per_view_alg = 559 * (v_sum / n) + 300 * P  # SURVEY 8(d) formula of the per-view kernel it replaces
     dram = None
     try:
-        dram = json.load(open(os.path.join(ROOT, "profiles", "r2b_traffic.json")))["preprocess_bwd_views"]
+        dram = json.load(open(os.path.join(ROOT, "profiles", "r2c_traffic.json")))["preprocess_bwd_views"]
     except Exception:
         pass
     return {"ms_per_launch": ms, "views_per_launch": n, "ms_per_view": ms / n, "alg_own_bytes": int(own),
             "dram_bytes": dram.get("dram_bytes_per_launch") if dram else None,
-            "dram_bytes_source": "profiles/r2b_traffic.json (ncu --set full, same workload)" if dram else None,
+            "dram_bytes_source": "profiles/r2c_traffic.json (ncu --set full, same workload)" if dram else None,
             "ncu_issue_active_pct": dram.get("issue_active_pct") if dram else None,
             "hbm_gbs": own / (ms * 1e-3) / 1e9, "hbm_frac": own / (ms * 1e-3) / 1e9 / hbm_peak,
             "bytes_of_the_per_view_kernels_it_replaces": int(per_view_alg * n),
@@ -503,7 +503,7 @@ def stage_table(torch, wl, steps, hbm_peak, sm_max_mhz):
     alg_own["sort"] = (4 + 16 * 4) * P + 16 * tile_passes * L            # depth sort + tile sort
     alg_own["tile_ranges"] = 4 * L + 8 * tiles
     cap = {}
-    for nm in ("r2b_traffic.json", "r2_traffic.json", "r1_traffic.json"):  # committed `ncu --set full` capture of one view (tools/ncu_traffic.py)
+    for nm in ("r2c_traffic.json", "r2b_traffic.json", "r2_traffic.json", "r1_traffic.json"):  # committed `ncu --set full` capture of one view (tools/ncu_traffic.py)
         try:
             cap = json.load(open(os.path.join(ROOT, "profiles", nm)))
             cap["_file"] = "profiles/" + nm

@@ -8,7 +8,7 @@ H, U = rows[0], rows[1]
 ki, ri, wi, ti = H.index("Kernel Name"), H.index("dram__bytes_read.sum"), H.index("dram__bytes_write.sum"), H.index("gpu__time_duration.sum")
 scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 acc = collections.defaultdict(list)
-STAGE = {"blend_bwd_kernel": "blend_bwd", "blend_fwd_kernel": "blend_fwd", "preprocess_fwd_kernel": "preprocess_fwd",
+STAGE = {"blend_bwd_kernel": "blend_bwd", "blend_fwd_kernel": "blend_fwd", "preprocess_fwd_kernel": "preprocess_fwd", "preprocess_fwd_views_kernel": "preprocess_fwd_views",
          "preprocess_bwd_kernel": "preprocess_bwd", "preprocess_bwd_views_kernel": "preprocess_bwd_views", "duplicate_tiles_kernel": "duplicate_keys", "tile_ranges_kernel": "tile_ranges",
          "onesweep_pass_kernel": "sort_pass", "scan_tiles_kernel": "scan"}
 for r in rows[2:]:

@@ -10,5 +10,5 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-c3 > gpurun_out/${T}_ncu_list.log 2>&1; echo list=$?
 timeout 900 ncu --set full --clock-control none --import-source on -k "regex:^(blend_|preprocess_|onesweep_|duplicate_tiles|tile_ranges|scan_tiles|sort_)" --launch-skip 45 -c 18 -f -o gpurun_out/${T}_full \
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-drop-in --no-c3 > gpurun_out/${T}_ncu_full.log 2>&1; echo full=$?
-timeout 600 ncu --set full --clock-control none --import-source on -k "regex:preprocess_bwd_views" --launch-skip 2 -c 2 -f -o gpurun_out/${T}_full_views \
+timeout 600 ncu --set full --clock-control none --import-source on -k "regex:preprocess_(bwd|fwd)_views" --launch-skip 2 -c 4 -f -o gpurun_out/${T}_full_views \
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-drop-in --no-c3 > gpurun_out/${T}_ncu_full_views.log 2>&1; echo full_views=$?
