@@ -304,3 +304,47 @@ def test_view_pipeline_grouped_preprocess_images_bit_identical(fuse_forward):
         for k in want:
             ok, worst = h.grad_close(got[k].cpu().numpy(), want[k].cpu().numpy(), **TOL)
             assert ok, (fuse_forward, rep, k, worst)
+
+
+@pytest.mark.parametrize("P,W,H", [(1, 16, 16), (3, 17, 33), (50, 1, 40), (300, 161, 7)])
+def test_grouped_paths_on_extreme_and_ragged_sizes(P, W, H):
+    """One Gaussian, images smaller than a tile, widths / heights that are not multiples of 16, and views of
+    DIFFERENT sizes inside one group: forward_views / backward_views / ViewPipeline against the per-view calls."""
+    from diff_gaussian_rasterization import views
+    from gsr_synth import ring_cameras
+    s = h.make_scene("tiny", P=P, width=W, height=H, seed=21)
+    s["means3D"] *= 0.3  # keep them in view
+    t = h.scene_tensors(s, requires_grad=False)
+    sizes = [(W, H), (W + 16, H), (W, H + 5)]
+    settings = []
+    for i, (w, hh) in enumerate(sizes):
+        sc = dict(s); sc["cam"] = ring_cameras(3, width=w, height=hh)[i]
+        settings.append(h.settings_for(sc))
+    kw = dict(shs=t["shs"], scales=t["scales"], rotations=t["rotations"])
+    rng = np.random.default_rng(P + W)
+    dLs = [torch.from_numpy(rng.standard_normal((3, rs.image_height, rs.image_width)).astype(np.float32)).cuda()
+           for rs in settings]
+    ref_imgs, states = [], []
+    for rs in settings:
+        img, radii, st = views.forward_view(rs, t["means3D"], t["opacities"], **kw)
+        ref_imgs.append(img); states.append(st)
+    want, _ = _per_view_reference(states, dLs, t)
+    got_fwd = views.forward_views(settings, t["means3D"], t["opacities"], **kw)
+    for (img, radii, st), ref_img, ref_st in zip(got_fwd, ref_imgs, states):
+        assert torch.equal(img, ref_img) and torch.equal(radii, ref_st.radii) and st.L == ref_st.L
+    g = {k: torch.full_like(v, 4.0) for k, v in t.items()}
+    views.backward_views([st for _, _, st in got_fwd], dLs, g, accumulate=False)
+    for k in want:
+        ok, worst = h.grad_close(g[k].cpu().numpy(), want[k].cpu().numpy(), **TOL)
+        assert ok, ("backward_views", k, worst)
+    vp = views.ViewPipeline()
+    g = {k: torch.full_like(v, 4.0) for k, v in t.items()}
+    imgs = []
+    vp.step(settings, lambda img, k: (imgs.append(img.clone()), dLs[k])[1], g, t["means3D"], t["opacities"],
+            overwrite=True, **kw)
+    torch.cuda.synchronize()
+    for a, b in zip(imgs, ref_imgs):
+        assert torch.equal(a, b)
+    for k in want:
+        ok, worst = h.grad_close(g[k].cpu().numpy(), want[k].cpu().numpy(), **TOL)
+        assert ok, ("pipeline", k, worst)
