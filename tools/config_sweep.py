@@ -49,6 +49,33 @@ def time_product(s, bwd, iters=3):
     return a.elapsed_time(b) / iters, stages, st.L, int((st.radii > 0).sum().item())
 
 
+def time_pipeline(s, bwd, n_views=8, iters=3):
+    """The same scene through views.ViewPipeline: `n_views` ring cameras per step, per-Gaussian work grouped over the
+    cameras, three streams (forward-only when bwd is False).  Returns ms per view."""
+    from gsr_synth import ring_cameras
+    t = h.scene_tensors(s, requires_grad=False)
+    W, H = s["cam"]["image_width"], s["cam"]["image_height"]
+    settings = []
+    for c in ring_cameras(n_views, width=W, height=H):
+        sc = dict(s); sc["cam"] = c
+        settings.append(h.settings_for(sc))
+    dL = torch.from_numpy(s["dL_dpix"]).cuda()
+    grads = {k: torch.zeros_like(v) for k, v in t.items()}
+    vp = views.ViewPipeline()
+    fn = (lambda img, k: dL) if bwd else (lambda img, k: None)
+    kw = dict(shs=t["shs"], scales=t["scales"], rotations=t["rotations"], overwrite=bwd)
+    vp.step(settings, fn, grads, t["means3D"], t["opacities"], **kw)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        vp.step(settings, fn, grads, t["means3D"], t["opacities"], **kw)
+    b.record()
+    torch.cuda.synchronize()
+    del vp
+    return a.elapsed_time(b) / iters / n_views
+
+
 def time_ref(s, bwd, iters=2):
     h.run_ref(s, grad=bwd, fetch=False)
     t0 = time.perf_counter()
@@ -66,6 +93,11 @@ def main():
         ms, stages, L, V = time_product(s, bwd)
         out.update(ms_per_view=round(ms, 3), views_per_s=round(1e3 / ms, 1), stages_ms=stages, L=int(L), V=V)
         torch.cuda.empty_cache()
+        if name != "C5":  # (C5: 1.5e9 pairs per view -- one view's lists at a time)
+            mp = time_pipeline(s, bwd)
+            out.update(pipeline_ms_per_view=round(mp, 3), pipeline_views_per_s=round(1e3 / mp, 1),
+                       pipeline="views.ViewPipeline, 8 ring cameras per step, grouped per-Gaussian kernels")
+            torch.cuda.empty_cache()
         g = h.run_gsr(s, grad=bwd, fetch=False)
         assert np.isfinite(g["color"]).all()
         if h.ref_available():
