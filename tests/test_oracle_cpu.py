@@ -179,3 +179,36 @@ def test_oracle_empty_and_all_culled():
     assert not vis.any()
     vis = cpu_ref.mark_visible(s["means3D"], s["cam"]["viewmatrix"], s["cam"]["projmatrix"])
     assert vis.all()
+
+
+def test_oracle_matches_reference_cuda_digest_at_C1():
+    """BASELINE configs[0] size (100k Gaussians SH3, 800x800, forward + backward): the CPU oracle against a digest of
+    the reference CUDA's own run on a B200 (tests/golden/c1_digest.npz, made by `tools/make_golden.py --digest`):
+    SHA-256 of every integer / index output (bit-exact: radii, tiles_touched, point_offsets, the 593k sorted 64-bit
+    keys, point_list, tile ranges, n_contrib), depth bits, image and final_T on a 4x4 pixel grid (<= 1e-5), every
+    64th row of each gradient and each gradient's float64 sums (the gradient tolerance of the other tests)."""
+    import hashlib
+    import os
+    z = np.load(os.path.join(h.GOLDEN_DIR, "c1_digest.npz"))
+    scene = h.make_scene("C1")
+    P, W, H, D = (int(x) for x in z["meta"])
+    assert (scene["P"], scene["cam"]["image_width"], scene["cam"]["image_height"], scene["sh_degree"]) == (P, W, H, D)
+    o = h.run_oracle(scene)
+    assert o["num_rendered"] == int(z["num_rendered"])
+    for k in INT_KEYS:
+        a = np.ascontiguousarray(o[k])
+        assert a.size == int(z["len_" + k]), k
+        assert hashlib.sha256(a.tobytes()).digest() == z["sha_" + k].tobytes(), k
+    assert np.array_equal(o["radii"][::64], z["radii_sub"])
+    vis = z["radii_sub"] > 0
+    assert np.array_equal(o["depths"].view(np.uint32)[::64][vis], z["depth_bits_sub"][vis])
+    assert np.abs(o["color"].reshape(3, H, W)[:, ::4, ::4] - z["color_sub"]).max() <= 1e-5
+    assert np.abs(o["final_T"].reshape(H, W)[::4, ::4] - z["final_T_sub"]).max() <= 1e-5
+    for k in ("means3D", "means2D", "opacity", "sh", "scales", "rotations"):
+        g = np.asarray(o["grads"][k]).reshape(P, -1)
+        ref_sub, gmax = z["grad_sub_" + k], float(z["grad_max_" + k])
+        sub = g[::64][:, : ref_sub.shape[1]]
+        tol = 1e-3 * np.abs(ref_sub) + 1e-4 * gmax
+        assert (np.abs(sub - ref_sub) <= tol).all(), (k, float((np.abs(sub - ref_sub) / tol).max()))
+        s_abs = float(z["grad_abs_" + k])
+        assert abs(float(g[:, : ref_sub.shape[1]].astype(np.float64).sum()) - float(z["grad_sum_" + k])) <= 1e-3 * s_abs, k
