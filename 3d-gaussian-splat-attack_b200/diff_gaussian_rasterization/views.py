@@ -639,6 +639,7 @@ class ViewPipeline:
             # (a single camera gains nothing from the grouped kernels: they run at lower occupancy than the per-view ones)
             fused = self.fuse > 1 and n > 1 and not raw_params and t["shs_rest"] is None and (M <= 16)
             self._step_grads = grads
+            self.pending = []  # (a previous step that raised part-way may have left deferred cameras behind)
             self.overwrite_next = bool(overwrite) and fused and grads.get("means2D") is None and \
                 any(g is not None for g in grads.values())
             if overwrite and not self.overwrite_next:
