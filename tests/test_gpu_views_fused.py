@@ -348,3 +348,32 @@ def test_grouped_paths_on_extreme_and_ragged_sizes(P, W, H):
     for k in want:
         ok, worst = h.grad_close(g[k].cpu().numpy(), want[k].cpu().numpy(), **TOL)
         assert ok, ("pipeline", k, worst)
+
+
+def test_view_pipeline_recovers_after_a_step_that_raised():
+    """dL_fn raising in the middle of a group leaves deferred cameras behind; the next step must not apply them."""
+    from diff_gaussian_rasterization import views
+    s = h.make_scene("tiny")
+    t = h.scene_tensors(s, requires_grad=False)
+    settings = _views_of(s, 5)
+    rng = np.random.default_rng(31)
+    dLs = [torch.from_numpy(rng.standard_normal((3, 120, 160)).astype(np.float32)).cuda() for _ in settings]
+    kw = dict(shs=t["shs"], scales=t["scales"], rotations=t["rotations"])
+    states = _forward_all(settings, t, **kw)
+    want, _ = _per_view_reference(states, dLs, t)
+    vp = views.ViewPipeline()
+    junk = {k: torch.zeros_like(v) for k, v in t.items()}
+
+    def bad(img, k):
+        if k == 3:
+            raise ValueError("loss failed")
+        return dLs[k] * 1000.0
+    with pytest.raises(ValueError):
+        vp.step(settings, bad, junk, t["means3D"], t["opacities"], **kw)
+    torch.cuda.synchronize()
+    got = {k: torch.full_like(v, 6.0) for k, v in t.items()}
+    vp.step(settings, lambda img, k: dLs[k], got, t["means3D"], t["opacities"], overwrite=True, **kw)
+    torch.cuda.synchronize()
+    for k in want:
+        ok, worst = h.grad_close(got[k].cpu().numpy(), want[k].cpu().numpy(), **TOL)
+        assert ok, (k, worst)
