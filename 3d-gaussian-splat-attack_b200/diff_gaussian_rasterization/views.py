@@ -374,8 +374,10 @@ class ViewPipeline:
         self.dev = dev
         self.overlap = overlap
         self.slots = [_PipeSlot(dev) for _ in range(n_slots)]
-        self.G = torch.cuda.Stream(dev, priority=-1) if overlap else None  # measured: 710 views/s vs 680 at equal priority
-        self.B = torch.cuda.Stream(dev, priority=-1) if overlap else None
+        import os
+        pg, pb = {"none": (0, 0), "g": (-1, 0), "b": (0, -1)}.get(os.environ.get("GSR_PIPE_PRIO", ""), (-1, -1))
+        self.G = torch.cuda.Stream(dev, priority=pg) if overlap else None  # measured: 710 views/s vs 680 at equal priority
+        self.B = torch.cuda.Stream(dev, priority=pb) if overlap else None
         self.scratch = torch.empty(0, dtype=torch.uint8, device=dev)
         n_order = self.fuse if (overlap and self.fuse_fwd and parallel_order) else 0
         self.O = [torch.cuda.Stream(dev, priority=-1) for _ in range(n_order)]  # ordering streams (grouped preprocess)
