@@ -362,6 +362,9 @@ class ViewPipeline:
         end up sharing hardware queues with compute streams (CUDA_DEVICE_MAX_CONNECTIONS = 8) and `e2e` halves."""
         if n_slots < 2:
             raise ValueError("n_slots must be >= 2")
+        import os
+        if os.environ.get("GSR_FUSE_VIEWS"):  # experiment knob: group size of the deferred / grouped kernels
+            fuse_backward = int(os.environ["GSR_FUSE_VIEWS"])
         self.fuse = max(1, min(int(fuse_backward), _abi.MAX_FUSED_VIEWS))
         self.fuse_fwd = bool(fuse_forward) and self.fuse > 1
         if self.fuse > 1:
