@@ -73,6 +73,14 @@ def forward_view(raster_settings, means3D, opacities, shs=None, colors_precomp=N
     return color, radii, ViewState(raster_settings, P, M, L, t, radii, geom, point_list, image, bool(raw_params))
 
 
+def _same_scene_settings(settings):
+    """The grouped kernels take the SH degree and the scale modifier once per group: every view must agree on them."""
+    if not settings:
+        return True
+    d0, m0 = int(settings[0].sh_degree), float(settings[0].scale_modifier)
+    return all(int(rs.sh_degree) == d0 and float(rs.scale_modifier) == m0 for rs in settings)
+
+
 def _view_fwd(inp, geom, radii):
     r = _abi.GsrViewFwd()
     r.viewmatrix, r.projmatrix, r.campos = inp.viewmatrix, inp.projmatrix, inp.campos
@@ -97,7 +105,7 @@ def forward_views(settings, means3D, opacities, shs=None, colors_precomp=None, s
     if not means3D.is_cuda:
         raise RuntimeError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
     P = means3D.size(0)
-    if P == 0 or any(rs.prefiltered for rs in settings):
+    if P == 0 or any(rs.prefiltered for rs in settings) or not _same_scene_settings(settings):
         return [forward_view(rs, means3D, opacities, shs=shs, colors_precomp=colors_precomp, scales=scales,
                              rotations=rotations, cov3D_precomp=cov3D_precomp) for rs in settings]
     dev = means3D.device
@@ -261,6 +269,8 @@ def backward_views(states, dL_dimages, grads: Dict[str, Optional[torch.Tensor]],
                     for k in ("means3D", "shs", "colors_precomp", "opacities", "scales", "rotations", "cov3D_precomp")):
             raise Exception("backward_views: all views must come from forward_view on the same input tensors, "
                             "without raw_params / shs_rest")
+    if not _same_scene_settings([st_.rs for st_ in states]):
+        raise Exception("backward_views: the views differ in sh_degree / scale_modifier; use backward_view per view")
     for k in grads:
         if k not in GRAD_KEYS:
             raise Exception(f"unknown gradient buffer '{k}' (expected one of {GRAD_KEYS})")
@@ -642,7 +652,8 @@ class ViewPipeline:
                 self.ev_start.record(R)
                 self.G.wait_event(self.ev_start)
             # (a single camera gains nothing from the grouped kernels: they run at lower occupancy than the per-view ones)
-            fused = self.fuse > 1 and n > 1 and not raw_params and t["shs_rest"] is None and (M <= 16)
+            fused = self.fuse > 1 and n > 1 and not raw_params and t["shs_rest"] is None and (M <= 16) and \
+                _same_scene_settings(settings)  # (SH degree and scale modifier are per-group inputs of the grouped kernels)
             self._step_grads = grads
             self.pending = []  # (a previous step that raised part-way may have left deferred cameras behind)
             self.overwrite_next = bool(overwrite) and fused and grads.get("means2D") is None and \

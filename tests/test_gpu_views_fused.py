@@ -377,3 +377,36 @@ def test_view_pipeline_recovers_after_a_step_that_raised():
     for k in want:
         ok, worst = h.grad_close(got[k].cpu().numpy(), want[k].cpu().numpy(), **TOL)
         assert ok, (k, worst)
+
+
+def test_views_that_differ_in_sh_degree_or_scale_modifier_are_not_grouped():
+    """sh_degree and scale_modifier are per-view settings in the reference API but per-group inputs of the grouped
+    kernels: mixed values must fall back to the per-view kernels (pipeline, forward_views) or be refused (backward_views)."""
+    from diff_gaussian_rasterization import views
+    s = h.make_scene("tiny")
+    t = h.scene_tensors(s, requires_grad=False)
+    base = _views_of(s, 3)
+    settings = [base[0], base[1]._replace(sh_degree=1), base[2]._replace(scale_modifier=0.7)]
+    kw = dict(shs=t["shs"], scales=t["scales"], rotations=t["rotations"])
+    rng = np.random.default_rng(41)
+    dLs = [torch.from_numpy(rng.standard_normal((3, 120, 160)).astype(np.float32)).cuda() for _ in settings]
+    ref_imgs, states = [], []
+    for rs in settings:
+        img, radii, st = views.forward_view(rs, t["means3D"], t["opacities"], **kw)
+        ref_imgs.append(img); states.append(st)
+    assert not torch.equal(ref_imgs[1], views.forward_view(base[1], t["means3D"], t["opacities"], **kw)[0])
+    want, _ = _per_view_reference(states, dLs, t)
+    for (img, radii, st), ref in zip(views.forward_views(settings, t["means3D"], t["opacities"], **kw), ref_imgs):
+        assert torch.equal(img, ref)
+    with pytest.raises(Exception):
+        views.backward_views(states, dLs, {k: torch.zeros_like(v) for k, v in t.items()})
+    got = {k: torch.zeros_like(v) for k, v in t.items()}
+    imgs = []
+    views.ViewPipeline().step(settings, lambda img, k: (imgs.append(img.clone()), dLs[k])[1], got, t["means3D"],
+                              t["opacities"], **kw)
+    torch.cuda.synchronize()
+    for a, b in zip(imgs, ref_imgs):
+        assert torch.equal(a, b)
+    for k in want:
+        ok, worst = h.grad_close(got[k].cpu().numpy(), want[k].cpu().numpy(), **TOL)
+        assert ok, (k, worst)
