@@ -18,7 +18,7 @@ namespace gsr {
 namespace {
 
 constexpr int FV_MAX = GSR_MAX_FUSED_VIEWS;
-constexpr int FV_THREADS = 256;
+constexpr int FV_THREADS = 128;  // (16 views x 3 x 128 floats of per-thread dL/dRGB = 24 KB of static shared memory)
 
 struct FusedViewDev {
   const float4* conic_opacity;
@@ -68,7 +68,7 @@ __device__ __forceinline__ void load_view_rows(ViewRows& r, const ViewShared& S,
 }
 
 template <bool ACC>
-__global__ void __launch_bounds__(FV_THREADS, 2)
+__global__ void __launch_bounds__(FV_THREADS, 4)  // 128 registers
 preprocess_bwd_views_kernel(gsr_inputs in, FusedViewsDev fv, float* __restrict__ dL_dopacity,
                             float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean3D,
                             float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh, float* __restrict__ dL_dscale,

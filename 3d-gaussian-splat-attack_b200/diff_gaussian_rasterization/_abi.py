@@ -14,7 +14,7 @@ CSRC_DIR = os.path.join(_ROOT, "csrc")
 
 GSR_OK, GSR_ERR_INVALID, GSR_ERR_CUDA, GSR_ERR_CAPACITY, GSR_ERR_PREFILTERED = 0, -1, -2, -3, -4
 ABI_VERSION = 4
-MAX_FUSED_VIEWS = 8  # GSR_MAX_FUSED_VIEWS
+MAX_FUSED_VIEWS = 16  # GSR_MAX_FUSED_VIEWS
 
 
 class GsrInputs(C.Structure):

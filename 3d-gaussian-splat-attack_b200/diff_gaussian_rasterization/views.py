@@ -91,7 +91,7 @@ def _view_fwd(inp, geom, radii):
 
 def forward_views(settings, means3D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
                   cov3D_precomp=None):
-    """Render SEVERAL views of the same Gaussians: the per-Gaussian preprocess runs once per group of up to 8 views
+    """Render SEVERAL views of the same Gaussians: the per-Gaussian preprocess runs once per group of up to 16 views
     (gsr_forward_preprocess_views: every Gaussian's attributes are read once instead of once per view), then each
     view is ordered, binned and blended as forward_view does.  Per view the results are bit-identical to
     forward_view's.  Returns a list of (color, radii, ViewState), usable with backward_view / backward_views."""
@@ -247,7 +247,7 @@ def _preprocess_views(lib, inp, refs, accumulate, grads, stream):
 def backward_views(states, dL_dimages, grads: Dict[str, Optional[torch.Tensor]], accumulate: bool = True,
                    means2D_grads=None) -> None:
     """Backward of SEVERAL forwarded views of the same Gaussians with the per-Gaussian half done once for all of
-    them (gsr_backward_blend_view per view, then gsr_backward_preprocess_views per group of up to 8 views): every
+    them (gsr_backward_blend_view per view, then gsr_backward_preprocess_views per group of up to 16 views): every
     Gaussian's attributes are read once and its gradient rows written once per group instead of once per view.
     `states` / `dL_dimages`: ViewStates of forward_view calls on the SAME input tensors and dL/dimage of each.
     accumulate=True ADDS the summed gradients to `grads` (as repeated backward_view calls would, up to summation

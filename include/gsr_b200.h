@@ -169,7 +169,7 @@ int gsr_backward_accumulate_phase(const gsr_inputs* in, const void* geom, const 
  *      cov3D_precomp); its camera fields are ignored, each view brings its own.  `views` is a HOST array.
  *      The fused-activation inputs (raw_params, shs_rest) and K > 0 are not supported here (GSR_ERR_INVALID).
  *      Results equal the sum of gsr_backward_accumulate over the views up to summation order. ---- */
-#define GSR_MAX_FUSED_VIEWS 8
+#define GSR_MAX_FUSED_VIEWS 16
 typedef struct gsr_view_ref {
   const float* viewmatrix;  /* the view's camera, as in gsr_inputs                                        */
   const float* projmatrix;

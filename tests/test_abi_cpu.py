@@ -57,7 +57,7 @@ int main(void) {
     R, F = _abi.GsrViewRef, _abi.GsrViewFwd
     assert got == [C.sizeof(_abi.GsrInputs), C.sizeof(R), R.geom.offset, R.dL_dmean2D.offset, C.sizeof(F), F.W.offset,
                    F.radii.offset]
-    assert _abi.MAX_FUSED_VIEWS == 8
+    assert _abi.MAX_FUSED_VIEWS == 16
 
 
 def test_higher_msb_matches_reference_semantics():

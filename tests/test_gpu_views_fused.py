@@ -46,9 +46,9 @@ def _per_view_reference(states, dLs, grads_like, with_m2=False):
     return ref, m2s
 
 
-@pytest.mark.parametrize("n_views", [1, 3, 8, 11])
+@pytest.mark.parametrize("n_views", [1, 3, 8, 11, 16, 19])
 def test_backward_views_equals_sum_of_per_view_backwards(n_views):
-    """SH degree 3, scale / rotation inputs; 11 views = one full group of 8 plus a group of 3."""
+    """SH degree 3, scale / rotation inputs; 19 views = one full group of 16 plus a group of 3."""
     from diff_gaussian_rasterization import views
     s = h.make_scene("small")
     t = h.scene_tensors(s, requires_grad=False)
@@ -155,10 +155,10 @@ def test_backward_views_argument_errors():
         views.backward_views([states[0], st2[0]], dLs, grads)
     # the C entry point rejects more than GSR_MAX_FUSED_VIEWS views per call
     lib = _abi.lib()
-    refs = (_abi.GsrViewRef * 9)()
+    refs = (_abi.GsrViewRef * 17)()
     inp = _abi.GsrInputs()
     inp.P = 1
-    assert lib.gsr_backward_preprocess_views(C.byref(inp), 9, refs, 1, *([None] * 7), None) == _abi.GSR_ERR_INVALID
+    assert lib.gsr_backward_preprocess_views(C.byref(inp), 17, refs, 1, *([None] * 7), None) == _abi.GSR_ERR_INVALID
     assert "views per call" in _abi.last_error()
 
 
@@ -211,11 +211,11 @@ def test_view_pipeline_fused_and_unfused_agree(fuse):
 
 def test_forward_views_is_bit_identical_to_forward_view():
     """gsr_forward_preprocess_views + gsr_forward_order against gsr_forward_geometry: the whole geometry state, radii,
-    duplicate count, point list and image of every view, byte for byte; 11 views = a group of 8 and a group of 3."""
+    duplicate count, point list and image of every view, byte for byte; 19 views = a group of 16 and a group of 3."""
     from diff_gaussian_rasterization import views
     s = h.make_scene("small")
     t = h.scene_tensors(s, requires_grad=False)
-    settings = _views_of(s, 11, W=320, H=240)
+    settings = _views_of(s, 19, W=320, H=240)
     kw = dict(shs=t["shs"], scales=t["scales"], rotations=t["rotations"])
     got = views.forward_views(settings, t["means3D"], t["opacities"], **kw)
     assert len(got) == len(settings)
@@ -273,11 +273,11 @@ def test_forward_views_precomputed_inputs_and_low_sh_degree():
 @pytest.mark.parametrize("fuse_forward", [True, False])
 def test_view_pipeline_grouped_preprocess_images_bit_identical(fuse_forward):
     """ViewPipeline with the grouped preprocess: images bit-identical to forward_view, gradients equal to per-view
-    sums; 19 cameras (more than the 18 slots of the ring), three steps, a camera without a backward."""
+    sums; 37 cameras (more than the 34 slots of the ring), three steps, a camera without a backward."""
     from diff_gaussian_rasterization import views
     s = h.make_scene("small")
     t = h.scene_tensors(s, requires_grad=False)
-    settings = _views_of(s, 19, W=320, H=240)
+    settings = _views_of(s, 37, W=320, H=240)
     rng = np.random.default_rng(23)
     dLs = [torch.from_numpy(rng.standard_normal((3, 240, 320)).astype(np.float32)).cuda() for _ in settings]
     kw = dict(shs=t["shs"], scales=t["scales"], rotations=t["rotations"])
