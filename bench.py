@@ -740,7 +740,11 @@ def run_gsr(args):
         "config": {"workload": f"{args.workload}: {wl.P} Gaussians SH3, {c['image_width']}x{c['image_height']}, fwd+bwd",
                    "views_per_rank_per_step": len(wl.cams), "parallelism": f"view-sharded x{world}, replicated Gaussians"
                    + (", NCCL all-reduce of attribute gradients per step" if world > 1 else ""),
-                   "l2": "inputs larger than L2 (236 MB of attributes + 25 MB dL/dpixel per view)", **counts},
+                   "l2": "inputs larger than L2 (236 MB of attributes + 25 MB dL/dpixel per view)",
+                   "step": ("every camera: depth order, binning, blend_fwd, blend_bwd; the per-Gaussian preprocess and its "
+                            "backward once per group of up to 16 cameras of the step (views.ViewPipeline)"
+                            if args.api == "views" and wl.overlap else "every camera on its own, one stream"),
+                   **counts},
         "e2e": e2e, "drop_in": drop_in, "extra": {"c3": None}, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "stages": stages,
     }
     if not args.no_cpu_baseline and world == 1:
